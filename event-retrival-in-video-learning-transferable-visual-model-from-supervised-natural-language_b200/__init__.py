@@ -1,0 +1,14 @@
+"""B200-native retrieval hot path: CLIP ViT encode_image + fused cosine scan/top-k (sm_100a CUDA behind a C ABI).
+
+Drop-in mirror of the reference's Python surface for this path:
+  clip            -- `clip.load / model.encode_image / model.visual.output_dim ...`  (openai/CLIP API)
+  embedding       -- legacy `extract_and_save_embeddings_from_folder`                (Backend/embedding.py:9)
+  services        -- `EmbeddingService`, `initialize_services` and the path/cache/data services it needs
+  search          -- FrameStore: HBM-resident fp16 store + fused top-k (single GPU and row-sharded)
+  vit             -- VisionEncoder: the hand-written tower behind `encode_image`
+The CUDA library (lib/libevr.so, built by __graft_entry__.build()) is required; there is no CPU fallback.
+"""
+from . import _lib  # noqa: F401  (fails loudly if libevr.so is missing)
+from . import search, vit  # noqa: F401
+
+__all__ = ["search", "vit", "_lib"]

@@ -1,0 +1,67 @@
+"""ctypes binding of lib/libevr.so -- the C ABI declared in include/evr.h."""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libevr.so")
+
+
+class EvrError(RuntimeError):
+    pass
+
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        f"{LIB_PATH} not found: build it with `python __graft_entry__.py` (nvcc, sm_100a). "
+        "This package has no CPU fallback.")
+
+lib = ctypes.CDLL(LIB_PATH)
+
+c_void_p, c_int, c_int64, c_size_t = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_size_t
+
+
+class VitCfg(ctypes.Structure):
+    _fields_ = [("image_size", c_int), ("patch", c_int), ("width", c_int), ("layers", c_int),
+                ("heads", c_int), ("out_dim", c_int)]
+
+
+# name -> (restype, argtypes); every symbol include/evr.h declares
+SIGNATURES = {
+    "evr_last_error": (ctypes.c_char_p, []),
+    "evr_version": (c_int, []),
+    "evr_launch_count": (c_int64, []),
+    "evr_store_prepare": (c_int, [c_void_p, c_int, c_int64, c_int, c_void_p, c_void_p]),
+    "evr_topk_workspace_bytes": (c_int, [c_int64, c_int, c_int, c_int, ctypes.POINTER(c_size_t)]),
+    "evr_topk_search": (c_int, [c_void_p, c_int64, c_int, c_int64, c_void_p, c_int, c_int, c_void_p, c_void_p,
+                                c_void_p, c_size_t, c_void_p]),
+    "evr_topk_merge": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "evr_rescore": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
+    "evr_vit_create": (c_int, [ctypes.POINTER(VitCfg), ctypes.POINTER(c_void_p), c_int, c_int,
+                               ctypes.POINTER(c_void_p)]),
+    "evr_vit_destroy": (c_int, [c_void_p]),
+    "evr_vit_encode": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_int, c_int, c_void_p]),
+    "evr_gemm_bf16": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
+}
+for _name, (_res, _args) in SIGNATURES.items():
+    _fn = getattr(lib, _name)
+    _fn.restype = _res
+    _fn.argtypes = _args
+
+
+def check(status, what):
+    if status != 0:
+        raise EvrError(f"{what} failed ({status}): {lib.evr_last_error().decode(errors='replace')}")
+
+
+def launch_count():
+    return int(lib.evr_launch_count())
+
+
+def current_stream_ptr():
+    import torch
+    return c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def ptr(t):
+    """Device (or host) pointer of a torch tensor as c_void_p; None -> NULL."""
+    return c_void_p(0 if t is None else t.data_ptr())

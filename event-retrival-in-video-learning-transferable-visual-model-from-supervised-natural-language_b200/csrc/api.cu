@@ -1,0 +1,73 @@
+// libevr.so: error string, version, launch counter, tensor-map encoding.
+#include <mutex>
+
+#include "../../include/evr.h"
+#include "common.cuh"
+
+namespace evr {
+
+static thread_local char g_err[1024] = "";
+std::atomic<int64_t> g_launches{0};
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+typedef CUresult (*encode_tiled_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static encode_tiled_fn get_encode() {
+  static encode_tiled_fn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<encode_tiled_fn>(p);
+  });
+  return fn;
+}
+
+int make_tmap_2d_16b(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t row_stride_bytes,
+                     uint32_t box_rows, bool is_bf16) {
+  encode_tiled_fn enc = get_encode();
+  EVR_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled not available from the driver");
+  EVR_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "tensor base %p not 16-B aligned", base);
+  EVR_REQUIRE(row_stride_bytes % 16 == 0, "row stride %llu not a multiple of 16 B",
+              (unsigned long long)row_stride_bytes);
+  EVR_REQUIRE(box_rows >= 1 && box_rows <= 256, "TMA box rows %u out of range", box_rows);
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {row_stride_bytes};
+  cuuint32_t box[2] = {64, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
+                   const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  EVR_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed: CUresult %d (rows %llu cols %llu stride %llu box %u)",
+              (int)r, (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)row_stride_bytes,
+              box_rows);
+  return 0;
+}
+
+int sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+  }
+  return n;
+}
+
+}  // namespace evr
+
+extern "C" {
+const char* evr_last_error(void) { return evr::g_err; }
+int evr_version(void) { return 100; }
+int64_t evr_launch_count(void) { return evr::g_launches.load(); }
+}

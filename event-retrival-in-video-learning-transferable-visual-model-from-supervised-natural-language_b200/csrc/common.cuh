@@ -1,0 +1,53 @@
+// Host-side plumbing shared by every translation unit of libevr.so:
+// error string, launch counter, TMA tensor-map encoding through the driver entry point.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+
+namespace evr {
+
+void set_error(const char* fmt, ...);
+extern std::atomic<int64_t> g_launches;
+inline void count_launch(int n = 1) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+#define EVR_CHECK_CUDA(expr)                                                                   \
+  do {                                                                                         \
+    cudaError_t e_ = (expr);                                                                   \
+    if (e_ != cudaSuccess) {                                                                   \
+      evr::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e_));    \
+      return 1;                                                                                \
+    }                                                                                          \
+  } while (0)
+
+#define EVR_REQUIRE(cond, ...)        \
+  do {                                \
+    if (!(cond)) {                    \
+      evr::set_error(__VA_ARGS__);    \
+      return 2;                       \
+    }                                 \
+  } while (0)
+
+// after a kernel launch: catches launch-configuration errors without synchronising
+#define EVR_CHECK_LAUNCH()                                                                     \
+  do {                                                                                         \
+    cudaError_t e_ = cudaGetLastError();                                                       \
+    if (e_ != cudaSuccess) {                                                                   \
+      evr::set_error("%s:%d: kernel launch -> %s", __FILE__, __LINE__, cudaGetErrorString(e_)); \
+      return 1;                                                                                \
+    }                                                                                          \
+    evr::count_launch();                                                                       \
+  } while (0)
+
+// 2-D row-major [rows, cols] 16-bit tensor, box = [box_rows, 64 cols] (=128 B inner), 128-B swizzle.
+// Out-of-bounds box elements are filled with zeros.
+int make_tmap_2d_16b(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t row_stride_bytes,
+                     uint32_t box_rows, bool is_bf16);
+
+int sm_count();
+
+}  // namespace evr

@@ -1,0 +1,254 @@
+// Persistent warp-specialised tcgen05 GEMM for the CLIP vision tower:
+//   out[M,N] = epilogue( A[M,K] (bf16, row-major) * W[N,K]^T (bf16, row-major) )
+// replaces the nn.Linear / nn.Conv2d(patch) / `x @ proj` library GEMMs issued by
+// openai/CLIP clip/model.py VisionTransformer.forward (SURVEY.md 2.2 K1,K4,K6-K9).
+//
+// One CTA per SM, 256 threads:
+//   warp 0  : TMA producer   (one elected lane)   global -> 128B-swizzled smem ring
+//   warp 1  : MMA issuer     (one elected lane)   tcgen05.mma kind::f16, fp32 accumulators in TMEM
+//   warp 2  : TMEM allocator
+//   warp 4-7: epilogue       tcgen05.ld -> registers -> fused bias/QuickGELU/residual -> global
+// Two TMEM accumulator stages let the epilogue of tile i overlap the MMAs of tile i+1.
+#pragma once
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace evr {
+
+enum GemmEpilogue : int {
+  EPI_BF16 = 0,       // out bf16 = acc + bias
+  EPI_BF16_GELU = 1,  // out bf16 = quickgelu(acc + bias)
+  EPI_F32_RESID = 2,  // out fp32 += acc + bias          (residual stream, in place)
+  EPI_F32 = 3,        // out fp32 = acc + bias
+  EPI_PATCH = 4,      // out fp32[token row] = acc + pos  (patch-embed: row remap b*P+p -> b*(P+1)+1+p)
+};
+
+struct GemmArgs {
+  int M, N, K;
+  const float* bias;  // [N] or nullptr
+  void* out;          // bf16 or fp32, row stride ldo elements
+  int ldo;
+  const float* pos;   // EPI_PATCH: positional_embedding [(P+1), N]
+  int patches;        // EPI_PATCH: P
+};
+
+constexpr int kGemmBlockM = 128;
+constexpr int kGemmBlockK = 64;  // 64 x 16-bit = one 128-B swizzle atom row
+constexpr int kGemmThreads = 256;
+
+template <int BLOCK_N>
+struct GemmCfg {
+  static constexpr int kABytes = kGemmBlockM * kGemmBlockK * 2;
+  static constexpr int kBBytes = BLOCK_N * kGemmBlockK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStages = (200 * 1024) / kStageBytes;
+  static constexpr int kTmemCols = (2 * BLOCK_N <= 32)    ? 32
+                                   : (2 * BLOCK_N <= 64)  ? 64
+                                   : (2 * BLOCK_N <= 128) ? 128
+                                   : (2 * BLOCK_N <= 256) ? 256
+                                                          : 512;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+  static_assert(BLOCK_N % 16 == 0 && BLOCK_N >= 32 && BLOCK_N <= 256, "invalid UMMA N");
+  static_assert(kBBytes % 1024 == 0, "B stage must keep 1024-B alignment for SWIZZLE_128B");
+  static_assert(kStages >= 3, "pipeline too shallow");
+};
+
+__device__ __forceinline__ float quick_gelu(float x) {
+  // clip/model.py QuickGELU: x * sigmoid(1.702 x)
+  return x * __frcp_rn(1.0f + __expf(-1.702f * x));
+}
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&t);
+}
+
+template <int BLOCK_N, int EPI>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+               const GemmArgs args) {
+  using Cfg = GemmCfg<BLOCK_N>;
+  constexpr int kStages = Cfg::kStages;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
+  uint64_t* full_bar = bars;                     // [kStages]  TMA -> MMA
+  uint64_t* empty_bar = bars + kStages;          // [kStages]  MMA -> TMA
+  uint64_t* tmem_full = bars + 2 * kStages;      // [2]        MMA -> epilogue
+  uint64_t* tmem_empty = bars + 2 * kStages + 2; // [2]        epilogue -> MMA
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int num_m = (args.M + kGemmBlockM - 1) / kGemmBlockM;
+  const int num_n = (args.N + BLOCK_N - 1) / BLOCK_N;
+  const int num_tiles = num_m * num_n;
+  const int num_kb = args.K / kGemmBlockK;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < kStages; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tmem_full[i], 1);
+      mbar_init(&tmem_empty[i], 4);  // one arrive per epilogue warp
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      // ===== TMA producer =====
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m_idx = tile % num_m, n_idx = tile / num_m;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * Cfg::kStageBytes;
+          uint8_t* sb = sa + Cfg::kABytes;
+          mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+          tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kGemmBlockK, m_idx * kGemmBlockM, kEvictNormal);
+          tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * kGemmBlockK, n_idx * BLOCK_N, kEvictLast);
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      // ===== MMA issuer =====
+      constexpr uint32_t idesc = umma_idesc_f16(/*bf16*/ 1, kGemmBlockM, BLOCK_N);
+      int stage = 0;
+      uint32_t phase = 0;
+      int as = 0;
+      uint32_t aphase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        mbar_wait(&tmem_empty[as], aphase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * BLOCK_N;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
+          const uint64_t a_desc = umma_smem_desc_sw128(sa);
+          const uint64_t b_desc = umma_smem_desc_sw128(sa + Cfg::kABytes);
+#pragma unroll
+          for (int k = 0; k < kGemmBlockK / 16; ++k) {
+            // 16 bf16 = 32 B along K inside the swizzle atom -> +2 in the (addr >> 4) field
+            umma_f16(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
+          }
+          umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs retire
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&tmem_full[as]);  // accumulator complete
+        as ^= 1;
+        if (as == 0) aphase ^= 1;
+      }
+    }
+  } else if (warp >= 4) {
+    // ===== epilogue: warp q owns TMEM lanes [32q, 32q+32) =====
+    const int q = warp - 4;
+    int as = 0;
+    uint32_t aphase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int m_idx = tile % num_m, n_idx = tile / num_m;
+      mbar_wait(&tmem_full[as], aphase);
+      tc_fence_after();
+      const int row = m_idx * kGemmBlockM + q * 32 + lane;
+      const bool row_ok = row < args.M;
+      size_t out_row = row;
+      const float* pos_row = nullptr;
+      if constexpr (EPI == EPI_PATCH) {
+        const int b = row / args.patches, p = row - b * args.patches;
+        out_row = static_cast<size_t>(b) * (args.patches + 1) + 1 + p;
+        pos_row = args.pos + static_cast<size_t>(1 + p) * args.N;
+      }
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N / 32; ++c) {
+        const int col0 = n_idx * BLOCK_N + c * 32;
+        if (col0 >= args.N) break;  // warp-uniform
+        uint32_t v[32];
+        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BLOCK_N + c * 32, v);
+        tmem_ld_wait();
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+        if (args.bias != nullptr) {
+          const float4* b4 = reinterpret_cast<const float4*>(args.bias + col0);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 b = __ldg(b4 + j);
+            f[4 * j] += b.x; f[4 * j + 1] += b.y; f[4 * j + 2] += b.z; f[4 * j + 3] += b.w;
+          }
+        }
+        if (row_ok) {
+          if constexpr (EPI == EPI_BF16 || EPI == EPI_BF16_GELU) {
+            if constexpr (EPI == EPI_BF16_GELU) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) f[j] = quick_gelu(f[j]);
+            }
+            uint4* o = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(args.out) + out_row * args.ldo + col0);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              uint4 w;
+              w.x = pack_bf16x2(f[8 * j], f[8 * j + 1]);
+              w.y = pack_bf16x2(f[8 * j + 2], f[8 * j + 3]);
+              w.z = pack_bf16x2(f[8 * j + 4], f[8 * j + 5]);
+              w.w = pack_bf16x2(f[8 * j + 6], f[8 * j + 7]);
+              o[j] = w;
+            }
+          } else {
+            float4* o = reinterpret_cast<float4*>(static_cast<float*>(args.out) + out_row * args.ldo + col0);
+            if constexpr (EPI == EPI_F32_RESID) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const float4 r = o[j];
+                f[4 * j] += r.x; f[4 * j + 1] += r.y; f[4 * j + 2] += r.z; f[4 * j + 3] += r.w;
+              }
+            }
+            if constexpr (EPI == EPI_PATCH) {
+              const float4* p4 = reinterpret_cast<const float4*>(pos_row + col0);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const float4 r = __ldg(p4 + j);
+                f[4 * j] += r.x; f[4 * j + 1] += r.y; f[4 * j + 2] += r.z; f[4 * j + 3] += r.w;
+              }
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[as]);
+      as ^= 1;
+      if (as == 0) aphase ^= 1;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+  }
+}
+
+// host launcher (gemm_tc.cu)
+int launch_gemm_bf16(const void* A, int lda, const void* W, int ldw, const GemmArgs& args, int epilogue,
+                     cudaStream_t stream);
+
+}  // namespace evr

@@ -1,0 +1,589 @@
+// Query-side hot path: store preparation (L2-normalise -> fp16), the fused cosine scan + top-k,
+// the final per-query select / cross-shard merge and the per-candidate re-score.
+//
+// Replaces (Backend/services/embedding_service.py):
+//   :210       embeddings / np.linalg.norm(embeddings, axis=-1, keepdims=True)     -> store_prepare
+//   :314 :365  similarities = np.dot(embeddings, q.T).flatten()                    -> topk_scan_kernel (MMA)
+//   :317-320   np.argsort(similarities)[::-1][:top_k]                              -> topk_scan_kernel epilogue
+//                                                                                     + topk_final_kernel
+//   :274-279   np.dot(embeddings[index:index+1], q.T)[0][0]                        -> rescore_kernel
+//
+// Scan kernel (one persistent CTA per SM, 192 threads):
+//   warp 0   TMA producer: the 128-query tile is made resident in smem (A operand); store rows stream
+//            through a 6-stage ring of [128 rows x 64 dims] 128B-swizzled tiles (B operand).
+//   warp 1   MMA issuer: tcgen05.mma kind::f16 (fp16 x fp16 -> fp32), D[128 queries x 128 rows] in TMEM,
+//            4 accumulator stages.
+//   warp 2-5 epilogue: TMEM lane = query, so every thread owns one query and sees 128 row scores per
+//            tile in registers.  A running threshold (the current k-th best) filters them; survivors are
+//            appended to a per-query candidate list in global memory (L2 resident).  When a list is
+//            nearly full the warp prunes it cooperatively to the exact top-k (bitwise binary search for
+//            the k-th key + stable ballot compaction) and raises the threshold.  The [Q, N] score matrix
+//            never exists in memory.
+#include <cuda_fp16.h>
+
+#include "../../include/evr.h"
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace evr {
+
+// ============================================================================ store preparation
+template <typename SrcT>
+__global__ void __launch_bounds__(256)
+store_prepare_kernel(const SrcT* __restrict__ src, int64_t N, int D, __half* __restrict__ dst) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t row = static_cast<int64_t>(blockIdx.x) * 8 + warp;
+  if (row >= N) return;
+  const SrcT* x = src + row * D;
+  float sq = 0.f;
+  for (int i = lane * 2; i < D; i += 64) {
+    float a, b;
+    if constexpr (sizeof(SrcT) == 4) {
+      const float2 t = *reinterpret_cast<const float2*>(x + i);
+      a = t.x; b = t.y;
+    } else {
+      const float2 t = __half22float2(*reinterpret_cast<const __half2*>(x + i));
+      a = t.x; b = t.y;
+    }
+    sq += a * a + b * b;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+  // zero rows stay zero (the reference would emit NaN: 0/0; compare_models.py:1168-1171 guards norm > 1e-8)
+  const float inv = sq > 0.f ? 1.0f / sqrtf(sq) : 0.f;
+  for (int i = lane * 2; i < D; i += 64) {
+    float a, b;
+    if constexpr (sizeof(SrcT) == 4) {
+      const float2 t = *reinterpret_cast<const float2*>(x + i);
+      a = t.x; b = t.y;
+    } else {
+      const float2 t = __half22float2(*reinterpret_cast<const __half2*>(x + i));
+      a = t.x; b = t.y;
+    }
+    *reinterpret_cast<__half2*>(dst + row * D + i) = __floats2half2_rn(a * inv, b * inv);
+  }
+}
+
+// ============================================================================ key mapping
+__device__ __forceinline__ uint32_t float_to_key(uint32_t bits) {  // monotone: larger float <=> larger key
+  return bits ^ (static_cast<uint32_t>(static_cast<int32_t>(bits) >> 31) | 0x80000000u);
+}
+__device__ __forceinline__ uint32_t key_to_float_bits(uint32_t key) {
+  return key ^ ((key >> 31) ? 0x80000000u : 0xFFFFFFFFu);
+}
+constexpr uint32_t kNegInfBits = 0xFF800000u;
+
+// ============================================================================ fused scan + top-k
+constexpr int kScanQTile = 128;     // queries per tile  (UMMA M, TMEM lanes)
+constexpr int kScanRowTile = 128;   // store rows per tile (UMMA N, TMEM columns per stage)
+constexpr int kScanStages = 6;      // smem ring depth, 16 KB per stage
+constexpr int kScanAccStages = 4;   // TMEM accumulator stages (4 x 128 = 512 columns)
+constexpr int kScanThreads = 192;
+constexpr int kScanStageBytes = kScanRowTile * 64 * 2;
+
+struct ScanArgs {
+  int64_t N;           // store rows on this GPU
+  int D, Q, k;
+  int num_qt;          // query tiles
+  int num_slices;      // store slices
+  int tiles_per_slice; // 128-row tiles per slice
+  int q_pad;           // num_qt * 128
+  int cap;             // candidate-list capacity per query (32 * EPL)
+  int2* cand;          // [grid][128][cap]  (score bits, local row)
+  float* part_score;   // [num_slices][q_pad][k]
+  int* part_idx;       // [num_slices][q_pad][k]
+};
+
+// Warp-cooperative exact prune of one query's candidate list to its top-k.  All 32 lanes call with the
+// same arguments.  Returns the key of the k-th best entry (new admission threshold).
+template <int EPL>
+__device__ __forceinline__ uint32_t warp_prune(int2* buf, int cnt, int k, int lane) {
+  uint32_t key[EPL];
+#pragma unroll
+  for (int i = 0; i < EPL; ++i) {
+    const int e = lane + 32 * i;
+    key[i] = e < cnt ? float_to_key(static_cast<uint32_t>(__ldcg(buf + e).x)) : 0u;
+  }
+  uint32_t T = 0;
+#pragma unroll 1
+  for (int bit = 31; bit >= 0; --bit) {
+    const uint32_t c = T | (1u << bit);
+    int n = 0;
+#pragma unroll
+    for (int i = 0; i < EPL; ++i) n += key[i] >= c;
+    n = __reduce_add_sync(0xffffffffu, n);
+    if (n >= k) T = c;
+  }
+  int n_gt = 0;
+#pragma unroll
+  for (int i = 0; i < EPL; ++i) n_gt += key[i] > T;
+  n_gt = __reduce_add_sync(0xffffffffu, n_gt);
+  const int need_eq = k - n_gt;
+  const uint32_t lt_mask = (1u << lane) - 1u;
+  int base = 0, eq_seen = 0;
+#pragma unroll
+  for (int i = 0; i < EPL; ++i) {
+    const int e = lane + 32 * i;
+    int2 ent = make_int2(0, 0);
+    if (e < cnt) ent = __ldcg(buf + e);
+    __syncwarp();  // every lane's load of this round lands before any lane's store below
+    const bool gt = key[i] > T, eq = key[i] == T;
+    const uint32_t m_eq = __ballot_sync(0xffffffffu, eq);
+    const bool take = gt || (eq && (eq_seen + __popc(m_eq & lt_mask) < need_eq));
+    const uint32_t m = __ballot_sync(0xffffffffu, take);  // also orders this round's loads before its stores
+    if (take) __stcg(buf + base + __popc(m & lt_mask), ent);
+    base += __popc(m);
+    eq_seen += __popc(m_eq);
+  }
+  __syncwarp();
+  return T;
+}
+
+template <int EPL>
+__global__ void __launch_bounds__(kScanThreads, 1)
+topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_s,
+                 const ScanArgs args) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int num_kb = args.D / 64;
+  const int q_bytes = kScanQTile * args.D * 2;
+  uint8_t* smem_q = smem;                 // [num_kb][128 x 64] swizzled, resident
+  uint8_t* smem_s = smem + q_bytes;       // [kScanStages][128 x 64]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_s + kScanStages * kScanStageBytes);
+  uint64_t* full_bar = bars;                                         // [kScanStages]
+  uint64_t* empty_bar = bars + kScanStages;                          // [kScanStages]
+  uint64_t* acc_full = bars + 2 * kScanStages;                       // [kScanAccStages]
+  uint64_t* acc_empty = bars + 2 * kScanStages + kScanAccStages;     // [kScanAccStages]
+  uint64_t* q_full = bars + 2 * kScanStages + 2 * kScanAccStages;    // [1]
+  uint64_t* q_empty = q_full + 1;                                    // [1]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(q_empty + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int num_items = args.num_qt * args.num_slices;
+  const int64_t total_tiles = (args.N + kScanRowTile - 1) / kScanRowTile;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_q);
+    tma_prefetch_desc(&tmap_s);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < kScanStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    for (int i = 0; i < kScanAccStages; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4); }
+    mbar_init(q_full, 1);
+    mbar_init(q_empty, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc<512>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      // ===== TMA producer =====
+      int stage = 0;
+      uint32_t phase = 0, qphase = 0;
+      for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+        const int qt = item % args.num_qt, slice = item / args.num_qt;
+        mbar_wait(q_empty, qphase ^ 1);  // MMAs of the previous item no longer read the query tile
+        mbar_expect_tx(q_full, q_bytes);
+        for (int kb = 0; kb < num_kb; ++kb)
+          tma_load_2d(smem_q + kb * kScanStageBytes, &tmap_q, q_full, kb * 64, qt * kScanQTile, kEvictLast);
+        qphase ^= 1;
+        const int64_t t0 = static_cast<int64_t>(slice) * args.tiles_per_slice;
+        int64_t t1 = t0 + args.tiles_per_slice;
+        if (t1 > total_tiles) t1 = total_tiles;
+        for (int64_t t = t0; t < t1; ++t) {
+          const int row = static_cast<int>(t * kScanRowTile);
+          for (int kb = 0; kb < num_kb; ++kb) {
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            mbar_expect_tx(&full_bar[stage], kScanStageBytes);
+            tma_load_2d(smem_s + stage * kScanStageBytes, &tmap_s, &full_bar[stage], kb * 64, row,
+                        args.num_qt > 1 ? kEvictNormal : kEvictFirst);
+            if (++stage == kScanStages) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      // ===== MMA issuer =====
+      constexpr uint32_t idesc = umma_idesc_f16(/*fp16*/ 0, kScanQTile, kScanRowTile);
+      int stage = 0, as = 0;
+      uint32_t phase = 0, aphase = 0, qphase = 0;
+      const uint32_t q_addr = smem_u32(smem_q);
+      for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+        const int slice = item / args.num_qt;
+        mbar_wait(q_full, qphase);
+        qphase ^= 1;
+        tc_fence_after();
+        const int64_t t0 = static_cast<int64_t>(slice) * args.tiles_per_slice;
+        int64_t t1 = t0 + args.tiles_per_slice;
+        if (t1 > total_tiles) t1 = total_tiles;
+        for (int64_t t = t0; t < t1; ++t) {
+          mbar_wait(&acc_empty[as], aphase ^ 1);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + as * kScanRowTile;
+          for (int kb = 0; kb < num_kb; ++kb) {
+            mbar_wait(&full_bar[stage], phase);
+            tc_fence_after();
+            const uint64_t a_desc = umma_smem_desc_sw128(q_addr + kb * kScanStageBytes);
+            const uint64_t b_desc = umma_smem_desc_sw128(smem_u32(smem_s + stage * kScanStageBytes));
+#pragma unroll
+            for (int k = 0; k < 4; ++k) umma_f16(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
+            umma_commit(&empty_bar[stage]);
+            if (++stage == kScanStages) { stage = 0; phase ^= 1; }
+          }
+          umma_commit(&acc_full[as]);
+          if (++as == kScanAccStages) { as = 0; aphase ^= 1; }
+        }
+        umma_commit(q_empty);
+      }
+    }
+  } else {
+    // ===== epilogue / selection: warps 2..5, TMEM lane quadrant = warp % 4 =====
+    const int quad = warp & 3;
+    const int k = args.k, cap = args.cap;
+    const int trigger = cap - kScanRowTile;
+    int as = 0;
+    uint32_t aphase = 0;
+    int2* const cand_warp = args.cand + (static_cast<size_t>(blockIdx.x) * kScanQTile + quad * 32) * cap;
+    int2* const buf = cand_warp + static_cast<size_t>(lane) * cap;
+    for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+      const int qt = item % args.num_qt, slice = item / args.num_qt;
+      const int q0 = qt * kScanQTile + quad * 32;  // first query of this warp
+      const bool q_valid = q0 + lane < args.Q;
+      float thresh = q_valid ? -INFINITY : INFINITY;
+      int cnt = 0;
+      const int64_t t0 = static_cast<int64_t>(slice) * args.tiles_per_slice;
+      int64_t t1 = t0 + args.tiles_per_slice;
+      if (t1 > total_tiles) t1 = total_tiles;
+      for (int64_t t = t0; t < t1; ++t) {
+        mbar_wait(&acc_full[as], aphase);
+        tc_fence_after();
+        const int row_base = static_cast<int>(t * kScanRowTile);
+        const int rows_left = static_cast<int>(args.N - row_base);  // > 0
+#pragma unroll 1
+        for (int c = 0; c < kScanRowTile / 32; ++c) {
+          uint32_t v[32];
+          tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + as * kScanRowTile + c * 32, v);
+          tmem_ld_wait();
+          float mx = __uint_as_float(v[0]);
+#pragma unroll
+          for (int j = 1; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(v[j]));
+          if (mx > thresh) {  // rare once the threshold has settled
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const int r = c * 32 + j;
+              if (__uint_as_float(v[j]) > thresh && r < rows_left) {
+                __stcg(buf + cnt, make_int2(static_cast<int>(v[j]), row_base + r));
+                ++cnt;
+              }
+            }
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&acc_empty[as]);  // release TMEM before any pruning
+        if (++as == kScanAccStages) { as = 0; aphase ^= 1; }
+
+        uint32_t need = __ballot_sync(0xffffffffu, cnt > trigger);
+        while (need) {
+          const int src = __ffs(need) - 1;
+          need &= need - 1;
+          const int c_src = __shfl_sync(0xffffffffu, cnt, src);
+          const uint32_t T = warp_prune<EPL>(cand_warp + static_cast<size_t>(src) * cap, c_src, k, lane);
+          if (lane == src) {
+            cnt = k;
+            thresh = __uint_as_float(key_to_float_bits(T));
+          }
+        }
+      }
+      // ---- item done: exact top-k of every query of this warp -> partial lists
+      __syncwarp();
+      for (int src = 0; src < 32; ++src) {
+        const int q = q0 + src;
+        if (q >= args.Q) break;  // warp-uniform
+        int c_src = __shfl_sync(0xffffffffu, cnt, src);
+        int2* b_src = cand_warp + static_cast<size_t>(src) * cap;
+        if (c_src > k) {
+          warp_prune<EPL>(b_src, c_src, k, lane);
+          c_src = k;
+        }
+        const size_t o = (static_cast<size_t>(slice) * args.q_pad + q) * k;
+        for (int j = lane; j < k; j += 32) {
+          int2 e = make_int2(static_cast<int>(kNegInfBits), -1);
+          if (j < c_src) e = __ldcg(b_src + j);
+          args.part_score[o + j] = __int_as_float(e.x);
+          args.part_idx[o + j] = e.y;
+        }
+      }
+      __syncwarp();
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc<512>(tmem_base);
+  }
+}
+
+// ============================================================================ final select / merge
+// One CTA per query: exact top-k of n = P*k candidates (P partial lists of k), sorted by
+// (score desc, index asc).  8-pass radix select on the 64-bit key (score key << 32 | ~idx),
+// then a bitonic sort of the k survivors in shared memory.
+template <typename IdxT>
+__global__ void __launch_bounds__(256)
+topk_final_kernel(const float* __restrict__ scores, const IdxT* __restrict__ idx, int P, int q_stride, int k,
+                  int64_t row_offset, float* __restrict__ out_scores, int64_t* __restrict__ out_idx) {
+  extern __shared__ __align__(16) uint8_t fsm[];
+  __shared__ unsigned hist[256];
+  __shared__ unsigned long long s_prefix;
+  __shared__ int s_remaining, s_count;
+  const int q = blockIdx.x;
+  const int n = P * k;
+  int kp = 1;
+  while (kp < k) kp <<= 1;
+  unsigned long long* skey = reinterpret_cast<unsigned long long*>(fsm);  // [kp]
+  long long* sidx = reinterpret_cast<long long*>(skey + kp);              // [kp]
+
+  auto load_key = [&](int e, long long& id) -> unsigned long long {
+    const int p = e / k, j = e - p * k;
+    const size_t off = (static_cast<size_t>(p) * q_stride + q) * k + j;
+    id = static_cast<long long>(idx[off]);
+    const uint32_t sk = float_to_key(__float_as_uint(scores[off]));
+    return (static_cast<unsigned long long>(sk) << 32) | static_cast<uint32_t>(~static_cast<uint32_t>(id));
+  };
+
+  if (threadIdx.x == 0) { s_prefix = 0ull; s_remaining = k; s_count = 0; }
+  __syncthreads();
+  unsigned long long himask = 0ull;
+  for (int shift = 56; shift >= 0; shift -= 8) {
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) hist[i] = 0;
+    __syncthreads();
+    const unsigned long long prefix = s_prefix;
+    for (int e = threadIdx.x; e < n; e += blockDim.x) {
+      long long id;
+      const unsigned long long key = load_key(e, id);
+      if ((key & himask) == prefix) atomicAdd(&hist[(key >> shift) & 255ull], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int rem = s_remaining, acc = 0, b = 255;
+      for (; b > 0; --b) {
+        if (acc + static_cast<int>(hist[b]) >= rem) break;
+        acc += hist[b];
+      }
+      s_remaining = rem - acc;
+      s_prefix = prefix | (static_cast<unsigned long long>(b) << shift);
+    }
+    himask |= 255ull << shift;
+    __syncthreads();
+  }
+  const unsigned long long T = s_prefix;  // k-th largest 64-bit key
+  for (int i = threadIdx.x; i < kp; i += blockDim.x) { skey[i] = 0ull; sidx[i] = -1; }
+  __syncthreads();
+  for (int e = threadIdx.x; e < n; e += blockDim.x) {
+    long long id;
+    const unsigned long long key = load_key(e, id);
+    if (key >= T) {
+      const int pos = atomicAdd(&s_count, 1);
+      if (pos < k) { skey[pos] = key; sidx[pos] = id; }
+    }
+  }
+  __syncthreads();
+  // bitonic sort, descending by key
+  for (int size = 2; size <= kp; size <<= 1) {
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      for (int i = threadIdx.x; i < kp; i += blockDim.x) {
+        const int j = i ^ stride;
+        if (j > i) {
+          const bool desc = (i & size) == 0;
+          const unsigned long long a = skey[i], b = skey[j];
+          if ((a < b) == desc) {
+            skey[i] = b; skey[j] = a;
+            const long long t = sidx[i]; sidx[i] = sidx[j]; sidx[j] = t;
+          }
+        }
+      }
+      __syncthreads();
+    }
+  }
+  for (int i = threadIdx.x; i < k; i += blockDim.x) {
+    const long long id = sidx[i];
+    out_scores[static_cast<size_t>(q) * k + i] = __uint_as_float(key_to_float_bits(static_cast<uint32_t>(skey[i] >> 32)));
+    out_idx[static_cast<size_t>(q) * k + i] = id < 0 ? -1 : id + row_offset;
+  }
+}
+
+// ============================================================================ re-score
+__global__ void __launch_bounds__(256)
+rescore_kernel(const __half* __restrict__ store, int64_t N, int D, const __half* __restrict__ query,
+               const int64_t* __restrict__ rows, int R, float* __restrict__ out) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int r = blockIdx.x * 8 + warp;
+  if (r >= R) return;
+  const int64_t row = rows[r];
+  float acc = 0.f;
+  if (row >= 0 && row < N) {
+    const __half* x = store + row * D;
+    for (int i = lane * 2; i < D; i += 64) {
+      const float2 a = __half22float2(*reinterpret_cast<const __half2*>(x + i));
+      const float2 b = __half22float2(*reinterpret_cast<const __half2*>(query + i));
+      acc += a.x * b.x + a.y * b.y;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if (lane == 0) out[r] = acc;
+}
+
+// ============================================================================ host side
+struct ScanPlan {
+  int epl, cap, num_qt, q_pad, num_slices, tiles_per_slice, grid;
+  size_t cand_bytes, part_score_bytes, part_idx_bytes, total_bytes;
+};
+
+static int plan_scan(int64_t N, int D, int Q, int k, ScanPlan* p) {
+  EVR_REQUIRE(N >= 1 && N < (int64_t(1) << 31) - 256, "top-k scan: N=%lld out of range", (long long)N);
+  EVR_REQUIRE(D % 64 == 0 && D >= 64 && D <= 512, "top-k scan: D=%d must be a multiple of 64 in [64, 512]", D);
+  EVR_REQUIRE(Q >= 1, "top-k scan: Q=%d", Q);
+  EVR_REQUIRE(k >= 1 && k <= 512, "top-k scan: k=%d must be in [1, 512]", k);
+  const int sms = sm_count();
+  p->epl = k <= 128 ? 16 : 64;
+  p->cap = 32 * p->epl;
+  p->num_qt = (Q + kScanQTile - 1) / kScanQTile;
+  p->q_pad = p->num_qt * kScanQTile;
+  const int64_t tiles = (N + kScanRowTile - 1) / kScanRowTile;
+  int S;
+  if (p->num_qt == 1) {
+    S = static_cast<int>(tiles < sms ? tiles : sms);
+  } else {
+    // several query tiles: pick the slice count whose item count quantises best onto the SMs
+    int best = 1;
+    double best_eff = -1.0;
+    const int max_s = static_cast<int>(tiles < 64 ? tiles : 64);
+    for (int s = 1; s <= max_s; ++s) {
+      const long long items = static_cast<long long>(p->num_qt) * s;
+      const long long rounds = (items + sms - 1) / sms;
+      double eff = static_cast<double>(items) / static_cast<double>(rounds * sms);
+      if (rounds < 2 && items < sms) eff *= 0.5;
+      if (eff > best_eff + 1e-9) { best_eff = eff; best = s; }
+    }
+    S = best;
+  }
+  p->tiles_per_slice = static_cast<int>((tiles + S - 1) / S);
+  p->num_slices = static_cast<int>((tiles + p->tiles_per_slice - 1) / p->tiles_per_slice);
+  const long long items = static_cast<long long>(p->num_qt) * p->num_slices;
+  p->grid = static_cast<int>(items < sms ? items : sms);
+  p->cand_bytes = static_cast<size_t>(p->grid) * kScanQTile * p->cap * sizeof(int2);
+  p->part_score_bytes = static_cast<size_t>(p->num_slices) * p->q_pad * k * sizeof(float);
+  p->part_idx_bytes = static_cast<size_t>(p->num_slices) * p->q_pad * k * sizeof(int);
+  auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
+  p->cand_bytes = up(p->cand_bytes);
+  p->part_score_bytes = up(p->part_score_bytes);
+  p->part_idx_bytes = up(p->part_idx_bytes);
+  p->total_bytes = p->cand_bytes + p->part_score_bytes + p->part_idx_bytes + 256;
+  return 0;
+}
+
+template <typename IdxT>
+static int launch_final(const float* scores, const IdxT* idx, int P, int q_stride, int Q, int k, int64_t row_offset,
+                        float* out_scores, int64_t* out_idx, cudaStream_t stream) {
+  int kp = 1;
+  while (kp < k) kp <<= 1;
+  const size_t smem = static_cast<size_t>(kp) * 16;
+  topk_final_kernel<IdxT><<<Q, 256, smem, stream>>>(scores, idx, P, q_stride, k, row_offset, out_scores, out_idx);
+  EVR_CHECK_LAUNCH();
+  return 0;
+}
+
+}  // namespace evr
+
+using namespace evr;
+
+extern "C" int evr_store_prepare(const void* src, int src_dtype, int64_t N, int D, void* dst_fp16, void* stream) {
+  EVR_REQUIRE(src && dst_fp16, "evr_store_prepare: null pointer");
+  EVR_REQUIRE(src_dtype == 0 || src_dtype == 1, "evr_store_prepare: src_dtype %d not in {0,1}", src_dtype);
+  EVR_REQUIRE(D >= 2 && D % 2 == 0, "evr_store_prepare: D=%d must be even", D);
+  if (N <= 0) return 0;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const unsigned blocks = static_cast<unsigned>((N + 7) / 8);
+  if (src_dtype == 0)
+    store_prepare_kernel<float><<<blocks, 256, 0, s>>>(static_cast<const float*>(src), N, D, static_cast<__half*>(dst_fp16));
+  else
+    store_prepare_kernel<__half><<<blocks, 256, 0, s>>>(static_cast<const __half*>(src), N, D, static_cast<__half*>(dst_fp16));
+  EVR_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int evr_topk_workspace_bytes(int64_t N, int D, int Q, int k, size_t* out_bytes) {
+  EVR_REQUIRE(out_bytes, "evr_topk_workspace_bytes: null out");
+  ScanPlan p;
+  if (int r = plan_scan(N, D, Q, k, &p)) return r;
+  *out_bytes = p.total_bytes;
+  return 0;
+}
+
+extern "C" int evr_topk_search(const void* store, int64_t N, int D, int64_t row_offset, const void* queries, int Q,
+                               int k, float* out_scores, int64_t* out_idx, void* workspace, size_t workspace_bytes,
+                               void* stream) {
+  EVR_REQUIRE(store && queries && out_scores && out_idx && workspace, "evr_topk_search: null pointer");
+  ScanPlan p;
+  if (int r = plan_scan(N, D, Q, k, &p)) return r;
+  EVR_REQUIRE(workspace_bytes >= p.total_bytes, "evr_topk_search: workspace %zu < required %zu", workspace_bytes,
+              p.total_bytes);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  uint8_t* ws = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~uintptr_t(255));
+  ScanArgs a{};
+  a.N = N; a.D = D; a.Q = Q; a.k = k;
+  a.num_qt = p.num_qt; a.num_slices = p.num_slices; a.tiles_per_slice = p.tiles_per_slice; a.q_pad = p.q_pad;
+  a.cap = p.cap;
+  a.cand = reinterpret_cast<int2*>(ws);
+  a.part_score = reinterpret_cast<float*>(ws + p.cand_bytes);
+  a.part_idx = reinterpret_cast<int*>(ws + p.cand_bytes + p.part_score_bytes);
+  CUtensorMap tq, ts;
+  if (int r = make_tmap_2d_16b(&tq, queries, Q, D, static_cast<uint64_t>(D) * 2, kScanQTile, false)) return r;
+  if (int r = make_tmap_2d_16b(&ts, store, N, D, static_cast<uint64_t>(D) * 2, kScanRowTile, false)) return r;
+  const int smem = kScanQTile * D * 2 + kScanStages * kScanStageBytes + 1024 + 256;
+  if (p.epl == 16) {
+    auto kern = topk_scan_kernel<16>;
+    static int cfg16 = 0;
+    if (smem > cfg16) {
+      EVR_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      cfg16 = smem;
+    }
+    kern<<<p.grid, kScanThreads, smem, s>>>(tq, ts, a);
+  } else {
+    auto kern = topk_scan_kernel<64>;
+    static int cfg64 = 0;
+    if (smem > cfg64) {
+      EVR_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      cfg64 = smem;
+    }
+    kern<<<p.grid, kScanThreads, smem, s>>>(tq, ts, a);
+  }
+  EVR_CHECK_LAUNCH();
+  return launch_final<int>(a.part_score, a.part_idx, p.num_slices, p.q_pad, Q, k, row_offset, out_scores, out_idx, s);
+}
+
+extern "C" int evr_topk_merge(const float* scores, const int64_t* idx, int P, int Q, int k, float* out_scores,
+                              int64_t* out_idx, void* stream) {
+  EVR_REQUIRE(scores && idx && out_scores && out_idx, "evr_topk_merge: null pointer");
+  EVR_REQUIRE(P >= 1 && Q >= 1 && k >= 1 && k <= 1024, "evr_topk_merge: bad shape P=%d Q=%d k=%d", P, Q, k);
+  return launch_final<int64_t>(scores, idx, P, Q, Q, k, 0, out_scores, out_idx, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int evr_rescore(const void* store, int64_t N, int D, const void* query_fp16, const int64_t* rows, int R,
+                           float* out, void* stream) {
+  EVR_REQUIRE(store && query_fp16 && rows && out, "evr_rescore: null pointer");
+  EVR_REQUIRE(D % 2 == 0, "evr_rescore: D must be even");
+  if (R <= 0) return 0;
+  rescore_kernel<<<(R + 7) / 8, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __half*>(store), N, D, static_cast<const __half*>(query_fp16), rows, R, out);
+  EVR_CHECK_LAUNCH();
+  return 0;
+}

@@ -1,0 +1,363 @@
+// Non-GEMM kernels of the CLIP vision tower: im2col(+normalise), cls rows, LayerNorm, attention core,
+// final L2-normalise/cast and the one-off weight repacking.  Structure follows openai/CLIP
+// clip/model.py VisionTransformer.forward / ResidualAttentionBlock.
+#include "vit_kernels.cuh"
+
+#include <cmath>
+
+namespace evr {
+
+// ----------------------------------------------------------------------------- im2col
+__constant__ float c_clip_mean[3] = {0.48145466f, 0.4578275f, 0.40821073f};
+__constant__ float c_clip_std[3] = {0.26862954f, 0.26130258f, 0.27577711f};
+
+__global__ void __launch_bounds__(256)
+im2col_kernel(const void* __restrict__ pixels, int pix_dtype, size_t total_pairs, int S, int p, int g, int K, int Kp,
+              __nv_bfloat16* __restrict__ out) {
+  const size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (idx >= total_pairs) return;
+  const int half_k = K >> 1;
+  const int col = 2 * static_cast<int>(idx % half_k);
+  const size_t row = idx / half_k;
+  const int pp = p * p;
+  const int c = col / pp, rem = col - c * pp;
+  const int ky = rem / p, kx = rem - ky * p;
+  const int gg = g * g;
+  const int b = static_cast<int>(row / gg), pr = static_cast<int>(row - static_cast<size_t>(b) * gg);
+  const int py = pr / g, px = pr - py * g;
+  const int y = py * p + ky, x = px * p + kx;
+  float v0, v1;
+  if (pix_dtype == 0) {
+    const float* src = static_cast<const float*>(pixels) + ((static_cast<size_t>(b) * 3 + c) * S + y) * S + x;
+    const float2 t = *reinterpret_cast<const float2*>(src);
+    v0 = t.x; v1 = t.y;
+  } else {
+    const uint8_t* src = static_cast<const uint8_t*>(pixels) + ((static_cast<size_t>(b) * S + y) * S + x) * 3 + c;
+    const float m = c_clip_mean[c], s = c_clip_std[c];
+    v0 = (static_cast<float>(src[0]) / 255.0f - m) / s;
+    v1 = (static_cast<float>(src[3]) / 255.0f - m) / s;
+  }
+  *reinterpret_cast<__nv_bfloat162*>(out + row * Kp + col) = __floats2bfloat162_rn(v0, v1);
+}
+
+int launch_im2col(const void* pixels, int pix_dtype, int B, int S, int p, int Kp, __nv_bfloat16* out,
+                  cudaStream_t stream) {
+  EVR_REQUIRE(S % p == 0 && p % 2 == 0, "im2col: image %d / patch %d unsupported", S, p);
+  const int g = S / p, K = 3 * p * p;
+  const size_t total = static_cast<size_t>(B) * g * g * (K / 2);
+  const unsigned blocks = static_cast<unsigned>((total + 255) / 256);
+  im2col_kernel<<<blocks, 256, 0, stream>>>(pixels, pix_dtype, total, S, p, g, K, Kp, out);
+  EVR_CHECK_LAUNCH();
+  return 0;
+}
+
+// ----------------------------------------------------------------------------- cls rows
+__global__ void cls_rows_kernel(float* __restrict__ x, const float* __restrict__ cls, const float* __restrict__ pos,
+                                int L, int d) {
+  float* row = x + static_cast<size_t>(blockIdx.x) * L * d;
+  for (int i = threadIdx.x; i < d; i += blockDim.x) row[i] = cls[i] + pos[i];
+}
+
+int launch_cls_rows(float* x, const float* cls, const float* pos, int B, int L, int d, cudaStream_t stream) {
+  cls_rows_kernel<<<B, 256, 0, stream>>>(x, cls, pos, L, d);
+  EVR_CHECK_LAUNCH();
+  return 0;
+}
+
+// ----------------------------------------------------------------------------- LayerNorm
+template <int D4, bool OUT_BF16>
+__global__ void __launch_bounds__(256)
+layernorm_kernel(const float* in, size_t in_stride, void* out, size_t out_stride,  // in may alias out (ln_pre)
+                 const float* __restrict__ gamma, const float* __restrict__ beta, int rows) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * 8 + warp;
+  if (row >= rows) return;
+  constexpr int d = D4 * 128;
+  const float4* x4 = reinterpret_cast<const float4*>(in + static_cast<size_t>(row) * in_stride);
+  float4 v[D4];
+  float sum = 0.f;
+#pragma unroll
+  for (int i = 0; i < D4; ++i) {
+    v[i] = x4[lane + 32 * i];
+    sum += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  const float mean = sum * (1.0f / d);
+  float sq = 0.f;
+#pragma unroll
+  for (int i = 0; i < D4; ++i) {
+    v[i].x -= mean; v[i].y -= mean; v[i].z -= mean; v[i].w -= mean;
+    sq += (v[i].x * v[i].x + v[i].y * v[i].y) + (v[i].z * v[i].z + v[i].w * v[i].w);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+  const float rstd = rsqrtf(sq * (1.0f / d) + 1e-5f);
+  const float4* g4 = reinterpret_cast<const float4*>(gamma);
+  const float4* b4 = reinterpret_cast<const float4*>(beta);
+#pragma unroll
+  for (int i = 0; i < D4; ++i) {
+    const float4 gm = __ldg(g4 + lane + 32 * i), bt = __ldg(b4 + lane + 32 * i);
+    float4 y;
+    y.x = v[i].x * rstd * gm.x + bt.x;
+    y.y = v[i].y * rstd * gm.y + bt.y;
+    y.z = v[i].z * rstd * gm.z + bt.z;
+    y.w = v[i].w * rstd * gm.w + bt.w;
+    if constexpr (OUT_BF16) {
+      __nv_bfloat162 lo = __floats2bfloat162_rn(y.x, y.y), hi = __floats2bfloat162_rn(y.z, y.w);
+      uint2 w;
+      w.x = *reinterpret_cast<uint32_t*>(&lo);
+      w.y = *reinterpret_cast<uint32_t*>(&hi);
+      reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(out) + static_cast<size_t>(row) * out_stride)[lane + 32 * i] = w;
+    } else {
+      reinterpret_cast<float4*>(static_cast<float*>(out) + static_cast<size_t>(row) * out_stride)[lane + 32 * i] = y;
+    }
+  }
+}
+
+int launch_layernorm(const float* in, size_t in_stride, void* out, size_t out_stride, int out_bf16,
+                     const float* gamma, const float* beta, int rows, int d, cudaStream_t stream) {
+  EVR_REQUIRE(d == 768 || d == 1024, "layernorm: width %d unsupported (768 | 1024)", d);
+  const int blocks = (rows + 7) / 8;
+  if (d == 768) {
+    if (out_bf16) layernorm_kernel<6, true><<<blocks, 256, 0, stream>>>(in, in_stride, out, out_stride, gamma, beta, rows);
+    else layernorm_kernel<6, false><<<blocks, 256, 0, stream>>>(in, in_stride, out, out_stride, gamma, beta, rows);
+  } else {
+    if (out_bf16) layernorm_kernel<8, true><<<blocks, 256, 0, stream>>>(in, in_stride, out, out_stride, gamma, beta, rows);
+    else layernorm_kernel<8, false><<<blocks, 256, 0, stream>>>(in, in_stride, out, out_stride, gamma, beta, rows);
+  }
+  EVR_CHECK_LAUNCH();
+  return 0;
+}
+
+// ----------------------------------------------------------------------------- attention core
+// One CTA per (head, image); K and V^T of the head staged in shared memory; each warp owns 16-query
+// tiles and runs a flash-style loop over 64-key blocks with mma.sync.m16n8k16 (bf16 in, fp32 acc).
+// The whole sequence (50 or 257 tokens) is far below one tcgen05 tile, and the core is ~1 % of the
+// tower's FLOPs, so it stays on the warp-level MMA path; no attention mask (vision tower).
+__device__ __forceinline__ void mma_bf16_16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t pack2_bf16(float lo, float hi) {
+  __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&t);
+}
+
+constexpr int kAttnKStride = 72;  // bf16 elements per K row in smem (64 + 8 pad: conflict-free fragments)
+
+__global__ void __launch_bounds__(128)
+attention_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, int L, int d, float scale) {
+  extern __shared__ __align__(16) uint8_t attn_smem[];
+  const int h = blockIdx.x, b = blockIdx.y;
+  const int Lp = (L + 63) & ~63;
+  const int vstride = Lp + 8;
+  __nv_bfloat16* Ks = reinterpret_cast<__nv_bfloat16*>(attn_smem);  // [Lp][72]
+  __nv_bfloat16* Vt = Ks + Lp * kAttnKStride;                       // [64][Lp + 8]
+  const size_t row0 = static_cast<size_t>(b) * L;
+  const int ld = 3 * d;
+
+  for (int i = threadIdx.x; i < Lp * 8; i += 128) {
+    const int r = i >> 3, c = i & 7;
+    uint4 kv = make_uint4(0, 0, 0, 0), vv = make_uint4(0, 0, 0, 0);
+    if (r < L) {
+      const __nv_bfloat16* base = qkv + (row0 + r) * ld + h * 64 + c * 8;
+      kv = *reinterpret_cast<const uint4*>(base + d);
+      vv = *reinterpret_cast<const uint4*>(base + 2 * d);
+    }
+    *reinterpret_cast<uint4*>(Ks + r * kAttnKStride + c * 8) = kv;
+    const __nv_bfloat16* ve = reinterpret_cast<const __nv_bfloat16*>(&vv);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) Vt[(c * 8 + j) * vstride + r] = ve[j];
+  }
+  __syncthreads();
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const int num_mt = (L + 15) >> 4;
+  for (int mt = warp; mt < num_mt; mt += 4) {
+    const int r0 = mt * 16 + g, r1 = r0 + 8;
+    uint32_t qa[4][4];
+    {
+      const __nv_bfloat16* q0 = qkv + (row0 + r0) * ld + h * 64;
+      const __nv_bfloat16* q1 = qkv + (row0 + r1) * ld + h * 64;
+#pragma unroll
+      for (int kk = 0; kk < 4; ++kk) {
+        qa[kk][0] = r0 < L ? *reinterpret_cast<const uint32_t*>(q0 + 16 * kk + 2 * t) : 0u;
+        qa[kk][1] = r1 < L ? *reinterpret_cast<const uint32_t*>(q1 + 16 * kk + 2 * t) : 0u;
+        qa[kk][2] = r0 < L ? *reinterpret_cast<const uint32_t*>(q0 + 16 * kk + 8 + 2 * t) : 0u;
+        qa[kk][3] = r1 < L ? *reinterpret_cast<const uint32_t*>(q1 + 16 * kk + 8 + 2 * t) : 0u;
+      }
+    }
+    float o[8][4];
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) { o[nt][0] = o[nt][1] = o[nt][2] = o[nt][3] = 0.f; }
+    float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+
+    for (int kb = 0; kb < Lp / 64; ++kb) {
+      float s[8][4];
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+        const __nv_bfloat16* kr = Ks + (kb * 64 + nt * 8 + g) * kAttnKStride;
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+          const uint32_t b0 = *reinterpret_cast<const uint32_t*>(kr + 16 * kk + 2 * t);
+          const uint32_t b1 = *reinterpret_cast<const uint32_t*>(kr + 16 * kk + 8 + 2 * t);
+          mma_bf16_16816(s[nt], qa[kk], b0, b1);
+        }
+      }
+      float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        const int col = kb * 64 + nt * 8 + 2 * t;
+        s[nt][0] = col < L ? s[nt][0] * scale : -INFINITY;
+        s[nt][1] = col + 1 < L ? s[nt][1] * scale : -INFINITY;
+        s[nt][2] = col < L ? s[nt][2] * scale : -INFINITY;
+        s[nt][3] = col + 1 < L ? s[nt][3] * scale : -INFINITY;
+        mx0 = fmaxf(mx0, fmaxf(s[nt][0], s[nt][1]));
+        mx1 = fmaxf(mx1, fmaxf(s[nt][2], s[nt][3]));
+      }
+      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+      const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);  // finite: every key block holds >= 1 valid key
+      const float a0 = __expf(m0 - mn0), a1 = __expf(m1 - mn1);
+      l0 *= a0; l1 *= a1;
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) { o[nt][0] *= a0; o[nt][1] *= a0; o[nt][2] *= a1; o[nt][3] *= a1; }
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        s[nt][0] = __expf(s[nt][0] - mn0);
+        s[nt][1] = __expf(s[nt][1] - mn0);
+        s[nt][2] = __expf(s[nt][2] - mn1);
+        s[nt][3] = __expf(s[nt][3] - mn1);
+        l0 += s[nt][0] + s[nt][1];
+        l1 += s[nt][2] + s[nt][3];
+      }
+      m0 = mn0; m1 = mn1;
+#pragma unroll
+      for (int kk = 0; kk < 4; ++kk) {
+        uint32_t pa[4];
+        pa[0] = pack2_bf16(s[2 * kk][0], s[2 * kk][1]);
+        pa[1] = pack2_bf16(s[2 * kk][2], s[2 * kk][3]);
+        pa[2] = pack2_bf16(s[2 * kk + 1][0], s[2 * kk + 1][1]);
+        pa[3] = pack2_bf16(s[2 * kk + 1][2], s[2 * kk + 1][3]);
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt) {
+          const __nv_bfloat16* vr = Vt + (nt * 8 + g) * vstride + kb * 64 + 16 * kk + 2 * t;
+          const uint32_t b0 = *reinterpret_cast<const uint32_t*>(vr);
+          const uint32_t b1 = *reinterpret_cast<const uint32_t*>(vr + 8);
+          mma_bf16_16816(o[nt], pa, b0, b1);
+        }
+      }
+    }
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+    const float i0 = 1.0f / l0, i1 = 1.0f / l1;
+    if (r0 < L) {
+      __nv_bfloat16* orow = out + (row0 + r0) * d + h * 64 + 2 * t;
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt)
+        *reinterpret_cast<uint32_t*>(orow + nt * 8) = pack2_bf16(o[nt][0] * i0, o[nt][1] * i0);
+    }
+    if (r1 < L) {
+      __nv_bfloat16* orow = out + (row0 + r1) * d + h * 64 + 2 * t;
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt)
+        *reinterpret_cast<uint32_t*>(orow + nt * 8) = pack2_bf16(o[nt][2] * i1, o[nt][3] * i1);
+    }
+  }
+}
+
+int launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int d, int heads,
+                     cudaStream_t stream) {
+  EVR_REQUIRE(heads * 64 == d, "attention: head dim must be 64 (d=%d heads=%d)", d, heads);
+  const int Lp = (L + 63) & ~63;
+  const size_t smem = static_cast<size_t>(Lp) * kAttnKStride * 2 + 64 * static_cast<size_t>(Lp + 8) * 2;
+  EVR_REQUIRE(smem <= 200 * 1024, "attention: sequence %d too long for the single-CTA K/V staging", L);
+  static size_t configured = 0;
+  if (smem > 48 * 1024 && smem > configured) {
+    EVR_CHECK_CUDA(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        static_cast<int>(smem)));
+    configured = smem;
+  }
+  attention_kernel<<<dim3(heads, B), 128, smem, stream>>>(qkv, out, L, d, 0.125f);
+  EVR_CHECK_LAUNCH();
+  return 0;
+}
+
+// ----------------------------------------------------------------------------- final normalise / cast
+__global__ void __launch_bounds__(256)
+l2norm_cast_kernel(const float* __restrict__ in, void* __restrict__ out, int out_dtype, int rows, int D,
+                   int normalise) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * 8 + warp;
+  if (row >= rows) return;
+  const float* x = in + static_cast<size_t>(row) * D;
+  float inv = 1.0f;
+  if (normalise) {
+    float sq = 0.f;
+    for (int i = lane; i < D; i += 32) sq += x[i] * x[i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+    inv = 1.0f / sqrtf(sq);
+  }
+  for (int i = lane; i < D; i += 32) {
+    const float y = normalise ? x[i] * inv : x[i];
+    if (out_dtype == 0) static_cast<float*>(out)[static_cast<size_t>(row) * D + i] = y;
+    else static_cast<__half*>(out)[static_cast<size_t>(row) * D + i] = __float2half_rn(y);
+  }
+}
+
+int launch_l2norm_cast(const float* in, void* out, int out_dtype, int rows, int D, int normalise,
+                       cudaStream_t stream) {
+  l2norm_cast_kernel<<<(rows + 7) / 8, 256, 0, stream>>>(in, out, out_dtype, rows, D, normalise);
+  EVR_CHECK_LAUNCH();
+  return 0;
+}
+
+// ----------------------------------------------------------------------------- weight repacking
+__global__ void cast_pad_bf16_kernel(const float* __restrict__ in, int rows, int cols, __nv_bfloat16* __restrict__ out,
+                                     int out_cols) {
+  const size_t total = static_cast<size_t>(rows) * out_cols;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const size_t r = i / out_cols;
+    const int c = static_cast<int>(i - r * out_cols);
+    out[i] = __float2bfloat16_rn(c < cols ? in[r * cols + c] : 0.f);
+  }
+}
+int launch_cast_pad_bf16(const float* in, int rows, int cols, __nv_bfloat16* out, int out_cols, cudaStream_t stream) {
+  cast_pad_bf16_kernel<<<1024, 256, 0, stream>>>(in, rows, cols, out, out_cols);
+  EVR_CHECK_LAUNCH();
+  return 0;
+}
+
+// in [rows, cols] fp32 -> out [cols, rows] bf16
+__global__ void transpose_cast_bf16_kernel(const float* __restrict__ in, int rows, int cols,
+                                           __nv_bfloat16* __restrict__ out) {
+  __shared__ float tile[32][33];
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+    const int r = r0 + j, c = c0 + threadIdx.x;
+    tile[j][threadIdx.x] = (r < rows && c < cols) ? in[static_cast<size_t>(r) * cols + c] : 0.f;
+  }
+  __syncthreads();
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+    const int c = c0 + j, r = r0 + threadIdx.x;
+    if (r < rows && c < cols) out[static_cast<size_t>(c) * rows + r] = __float2bfloat16_rn(tile[threadIdx.x][j]);
+  }
+}
+int launch_transpose_cast_bf16(const float* in, int rows, int cols, __nv_bfloat16* out, cudaStream_t stream) {
+  dim3 grid((cols + 31) / 32, (rows + 31) / 32);
+  transpose_cast_bf16_kernel<<<grid, dim3(32, 8), 0, stream>>>(in, rows, cols, out);
+  EVR_CHECK_LAUNCH();
+  return 0;
+}
+
+}  // namespace evr

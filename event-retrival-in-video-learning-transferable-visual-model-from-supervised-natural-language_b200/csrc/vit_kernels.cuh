@@ -1,0 +1,35 @@
+// Non-GEMM kernels of the CLIP vision tower (declarations; definitions in vit_kernels.cu).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
+#include "common.cuh"
+
+namespace evr {
+
+// pixels -> bf16 im2col matrix [B*g*g, Kp]; col = c*p*p + ky*p + kx (conv1.weight flattening).
+// pix_dtype 0: fp32 NCHW already normalised; 1: uint8 NHWC, (x/255 - mean)/std fused (clip._transform).
+int launch_im2col(const void* pixels, int pix_dtype, int B, int S, int p, int Kp, __nv_bfloat16* out,
+                  cudaStream_t stream);
+
+// x[b*L, :] = class_embedding + positional_embedding[0]
+int launch_cls_rows(float* x, const float* cls, const float* pos, int B, int L, int d, cudaStream_t stream);
+
+// LayerNorm over the last dim (fp32 statistics, eps 1e-5, clip/model.py LayerNorm).
+// in: fp32 rows at in + r*in_stride; out: bf16 (out_bf16 != 0) or fp32 rows at out + r*out_stride.
+int launch_layernorm(const float* in, size_t in_stride, void* out, size_t out_stride, int out_bf16,
+                     const float* gamma, const float* beta, int rows, int d, cudaStream_t stream);
+
+// softmax(q k^T / sqrt(hd)) v per (image, head); qkv bf16 [B*L, 3d] (q | k | v), out bf16 [B*L, d]. hd = 64.
+int launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int d, int heads,
+                     cudaStream_t stream);
+
+// out[r] = in[r] (/ ||in[r]||) ; out fp32 (out_dtype 0) or fp16 (1)
+int launch_l2norm_cast(const float* in, void* out, int out_dtype, int rows, int D, int normalise,
+                       cudaStream_t stream);
+
+// weight repacking (once, at handle creation)
+int launch_cast_pad_bf16(const float* in, int rows, int cols, __nv_bfloat16* out, int out_cols, cudaStream_t stream);
+int launch_transpose_cast_bf16(const float* in, int rows, int cols, __nv_bfloat16* out, cudaStream_t stream);
+
+}  // namespace evr

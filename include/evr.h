@@ -1,0 +1,95 @@
+/* libevr.so -- C ABI of the B200-native retrieval hot path.
+ *
+ * The reference has no FFI layer; its operator API for this path is a set of Python
+ * callables.  Each entry point below names the reference call it
+ * replaces.  All pointers are DEVICE pointers unless the name ends in _host.  Every
+ * function returns 0 on success, non-zero on error (message: evr_last_error()).
+ * `stream` is a cudaStream_t passed as void*.  No C++ types cross this boundary.
+ */
+#ifndef EVR_H_
+#define EVR_H_
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* evr_last_error(void);
+int evr_version(void);
+/* number of kernels launched by this library since load (bench.py's gpu_launches) */
+int64_t evr_launch_count(void);
+
+/* ---- store preparation -------------------------------------------------------------
+ * replaces  embeddings / np.linalg.norm(embeddings, axis=-1, keepdims=True)
+ *           Backend/services/embedding_service.py:210 (get_embeddings)
+ * src: [N, D] fp32 (src_dtype 0) or fp16 (src_dtype 1), row-major.
+ * dst: [N, D] fp16 unit-norm rows (the HBM-resident store the scan streams).
+ * fp16 sources follow numpy's fp16 semantics closely: norm accumulated in fp32, the
+ * quotient rounded to fp16.  Zero rows stay zero (compare_models.py:1168-1171 guard). */
+int evr_store_prepare(const void* src, int src_dtype, int64_t N, int D, void* dst_fp16, void* stream);
+
+/* ---- fused cosine scan + top-k -------------------------------------------------------
+ * replaces  np.dot(embeddings, q.T).flatten() ; np.argsort(sim)[::-1][:top_k]
+ *           Backend/services/embedding_service.py:314-320 and :365-371
+ * store   [N, D] fp16 (from evr_store_prepare), D % 64 == 0, D <= 512
+ * queries [Q, D] fp16
+ * out_scores [Q, k] fp32 descending; out_idx [Q, k] int64 = row_offset + local row.
+ * If k > N the tail is filled with score -inf / idx -1.
+ * workspace: evr_topk_workspace_bytes(N, D, Q, k) bytes of device memory. */
+int evr_topk_workspace_bytes(int64_t N, int D, int Q, int k, size_t* out_bytes);
+int evr_topk_search(const void* store, int64_t N, int D, int64_t row_offset, const void* queries, int Q, int k,
+                    float* out_scores, int64_t* out_idx, void* workspace, size_t workspace_bytes, void* stream);
+
+/* P-way merge of per-shard sorted lists (after the NCCL all-gather of section 8e).
+ * scores [P, Q, k] fp32, idx [P, Q, k] int64  ->  out [Q, k]. */
+int evr_topk_merge(const float* scores, const int64_t* idx, int P, int Q, int k, float* out_scores,
+                   int64_t* out_idx, void* stream);
+
+/* per-candidate re-score: replaces np.dot(embeddings[i:i+1], q.T)[0][0]
+ * (embedding_service.py:274-279).  rows [R] int64 local row ids; out [R] fp32. */
+int evr_rescore(const void* store, int64_t N, int D, const void* query_fp16, const int64_t* rows, int R,
+                float* out, void* stream);
+
+/* ---- CLIP vision tower (encode_image) ------------------------------------------------
+ * replaces  model.encode_image(batch)  -> VisionTransformer.forward of openai/CLIP
+ *           call sites Backend/embedding.py:49, services/embedding_service.py:41,414,490 */
+typedef struct evr_vit evr_vit;
+typedef struct {
+  int image_size; /* 224 */
+  int patch;      /* 32 | 16 | 14 */
+  int width;      /* 768 | 1024 */
+  int layers;     /* 12 | 24 */
+  int heads;      /* 12 | 16 */
+  int out_dim;    /* 512 | 768 */
+} evr_vit_cfg;
+
+/* Weight order (fp32 device pointers, openai state_dict keys):
+ *   0 conv1.weight [d,3,p,p]  1 class_embedding [d]  2 positional_embedding [L,d]
+ *   3 ln_pre.weight 4 ln_pre.bias
+ *   per layer i, base 5 + 12*i:
+ *     +0 ln_1.weight +1 ln_1.bias +2 attn.in_proj_weight [3d,d] +3 attn.in_proj_bias
+ *     +4 attn.out_proj.weight [d,d] +5 attn.out_proj.bias +6 ln_2.weight +7 ln_2.bias
+ *     +8 mlp.c_fc.weight [4d,d] +9 mlp.c_fc.bias +10 mlp.c_proj.weight [d,4d] +11 mlp.c_proj.bias
+ *   then ln_post.weight, ln_post.bias, proj [d,out]
+ * Weights are repacked once (bf16, K-major) into memory owned by the handle. */
+int evr_vit_create(const evr_vit_cfg* cfg, const void* const* weights_fp32, int n_weights, int max_batch,
+                   evr_vit** out);
+int evr_vit_destroy(evr_vit* h);
+/* pixels: [B,3,S,S] fp32 already normalised (pix_dtype 0), or [B,S,S,3] uint8 RGB
+ * (pix_dtype 1: /255 + CLIP mean/std fused on device, clip._transform's ToTensor+Normalize).
+ * out: [B, out_dim] fp32 (out_dtype 0) or fp16 (out_dtype 1); l2_normalise != 0 applies
+ * x / ||x|| (embedding_service.py:45,502). */
+int evr_vit_encode(evr_vit* h, const void* pixels, int pix_dtype, int B, void* out, int out_dtype,
+                   int l2_normalise, void* stream);
+
+/* building-block GEMM exported for the parity tests:  C[M,N] = A[M,K] * W[N,K]^T (+bias)
+ * A, W bf16 row-major; epilogue 0: bf16 out (+bias), 1: bias+QuickGELU bf16,
+ * 2: fp32 out = acc + bias + residual (in place on out). */
+int evr_gemm_bf16(const void* A, const void* W, const float* bias, void* out, int M, int N, int K, int epilogue,
+                  void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EVR_H_ */
