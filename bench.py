@@ -1,0 +1,466 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the retrieval hot path on B200 (contract: see DESIGN.md "Measurement").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload both|encode|search]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus N --steps K --warmup W
+
+Primary line (BASELINE.json configs[1]): ViT-B/32 key-frame encode, batch 256 synthetic frames per GPU, bf16 tensor
+cores.  A step = one batch of 256 frames through evr_vit_encode; value = frames/s over all ranks with the uint8
+frames already resident in HBM; e2e = the same through the public host API (pinned uint8 frames -> H2D -> encode ->
+D2H of the embeddings inside the timed region).
+Nested "search" object (BASELINE.json configs[2], configs[3] for N > 1): fused cosine scan + top-100,
+10 000 queries x 10 M x 512 fp16 rows on one GPU (100 M rows row-sharded + NCCL all-gather + merge for N > 1), plus
+the HBM-bound small-query-batch regime.
+
+--impl reference times the reference's own CPU path (its algorithm restated in oracle/, see DESIGN.md: the `clip`
+dependency of the reference is an absent submodule) on the host cores, on a bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "frames/s ViT-B/32 encode"
+SEARCH_METRIC = "queries/s top-100 over 10M-frame store"
+VIT_NAME = "ViT-B/32"
+
+
+# ----------------------------------------------------------------------------------------------- helpers
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"hbm_gbs": d["hbm_gbs"], "tf_burst": d["bf16_tflops"], "tf_sustained": d["bf16_tflops_sustained"],
+                "source": "measured (MEASURED_PEAKS.json)"}
+    return {"hbm_gbs": 6650.0, "tf_burst": 1590.0, "tf_sustained": 1400.0, "source": "fallback (B200_PROFILING.md)"}
+
+
+def vit_flops_per_frame(name):
+    """(total, gemm-family) algorithmic FLOPs per frame; SURVEY.md 8d / BASELINE.md section 3."""
+    g = {"ViT-B/32": (224, 32, 768, 12, 12, 512), "ViT-L/14": (224, 14, 1024, 24, 16, 768)}[name]
+    S, p, d, layers, heads, out = g
+    P = (S // p) ** 2
+    L = P + 1
+    patch = 2.0 * P * 3 * p * p * d
+    per_layer_gemm = 2.0 * L * d * (3 * d + d + 4 * d + 4 * d)
+    attn = 2.0 * 2.0 * heads * L * L * (d // heads)
+    proj = 2.0 * d * out
+    gemm = patch + layers * per_layer_gemm + proj
+    return gemm + layers * attn, gemm
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled every 200 ms during the timed region (B200_PROFILING.md)."""
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
+                 "-lms", "200"], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, reasons, mx = [], set(), None
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in open(self.path):
+            parts = [x.strip() for x in line.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx = float(parts[1])
+            except ValueError:
+                continue
+            for nm, val in zip(names, parts[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        os.unlink(self.path)
+        if sm:
+            busy = sorted(sm)[len(sm) // 2:]  # upper half = samples under load
+            out.update(sm_mhz=statistics.median(busy), sm_max_mhz=mx, reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+def dist_env():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+def max_over_ranks(x, device, world):
+    import torch
+    import torch.distributed as dist
+    if world == 1:
+        return x
+    t = torch.tensor([x], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def barrier_sync(world):
+    import torch
+    import torch.distributed as dist
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+# ----------------------------------------------------------------------------------------------- encode (ours)
+def bench_encode(pkg, vo, dev, rank, world, steps, warmup, batch, peaks):
+    import torch
+    _lib = pkg._lib
+    visual = vo.build_visual(VIT_NAME, seed=1)  # seeded random init, openai scales (no weights on the box)
+    enc = pkg.vit.VisionEncoder.from_state_dict(visual.state_dict(), VIT_NAME, device=dev, max_batch=batch)
+    # synthetic uint8 RGB frames; R distinct batches so consecutive steps never reuse L2 lines
+    R = 8
+    g = torch.Generator(device="cpu").manual_seed(1000 + rank)
+    host = [torch.randint(0, 256, (batch, 224, 224, 3), generator=g, dtype=torch.uint8).pin_memory() for _ in range(R)]
+    resident = [h.to(dev) for h in host]
+    out = None
+    for i in range(warmup):
+        out = enc.encode(resident[i % R], normalise=True)
+    barrier_sync(world)
+    sampler = ClockSampler(dev.index)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.25)
+    launches0 = _lib.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier_sync(world)
+    e0.record()
+    for i in range(steps):
+        out = enc.encode(resident[i % R], normalise=True)
+    e1.record()
+    barrier_sync(world)
+    ms = max_over_ranks(e0.elapsed_time(e1), dev, world)
+    launches = _lib.launch_count() - launches0
+    clocks = sampler.stop() if rank == 0 else None
+    assert torch.isfinite(out).all()
+
+    # ---- end to end through the public host API: pinned uint8 frames -> H2D -> tower -> D2H embeddings
+    for _ in enc.encode_stream((host[i % R] for i in range(max(warmup, 3))), normalise=True):
+        pass
+    barrier_sync(world)
+    t0 = time.perf_counter()
+    e0.record()
+    n_out = 0
+    for emb in enc.encode_stream((host[i % R] for i in range(steps)), normalise=True):
+        n_out += emb.shape[0]
+    e1.record()
+    barrier_sync(world)
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    e2e_ms = max_over_ranks(max(e0.elapsed_time(e1), wall_ms), dev, world)
+    assert n_out == steps * batch
+
+    # ---- per-family kernel time (separate pass of the same K steps; CUDA events around every launch)
+    roof = None
+    if rank == 0:
+        _lib.profile_enable(True)
+        for i in range(steps):
+            enc.encode(resident[i % R], normalise=True)
+        torch.cuda.synchronize()
+        fam = _lib.profile_read()
+        _lib.profile_enable(False)
+        total_flops, gemm_flops = vit_flops_per_frame(VIT_NAME)
+        gemm_ms, gemm_n = fam["gemm_tc"]
+        all_ms = sum(v[0] for v in fam.values())
+        achieved = gemm_flops * batch * steps / (gemm_ms * 1e-3) / 1e12
+        roof = {
+            "bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05, all ViT GEMMs)",
+            "achieved": round(achieved, 1), "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
+            "frac": round(achieved / peaks["tf_sustained"], 4), "traffic": None,
+            "peak_source": peaks["source"] + ", sustained bf16",
+            "flops_per_launch_avg": gemm_flops * batch * steps / max(gemm_n, 1),
+            "avg_launch_ms": round(gemm_ms / max(gemm_n, 1), 5),
+            "share_of_step": round(gemm_ms / all_ms, 4),
+            "whole_step_frac": round(total_flops * batch * world * steps / (ms * 1e-3) / 1e12 / world
+                                     / peaks["tf_sustained"], 4),
+            "family_ms_per_step": {k: round(v[0] / steps, 4) for k, v in fam.items() if v[1]},
+            "timing": "CUDA events around every launch, separate pass of the same K steps",
+        }
+    frames = batch * world * steps
+    return {
+        "value": frames / (ms * 1e-3), "ms_per_step": ms / steps, "gpu_launches": int(launches), "clocks": clocks,
+        "e2e": {"value": round(frames / (e2e_ms * 1e-3), 1), "unit": "frames/s",
+                "h2d_bytes_per_step": batch * 224 * 224 * 3, "d2h_bytes_per_step": batch * 512 * 4,
+                "api": "VisionEncoder.encode_stream(pinned uint8 [256,224,224,3]) -> host fp32 [256,512]"},
+        "roofline": roof,
+    }
+
+
+# ----------------------------------------------------------------------------------------------- search (ours)
+def make_store(torch, dev, n_rows, seed):
+    """[n_rows, 512] unit-norm fp16 rows generated on the device (N(0,1) -> L2 normalise -> fp16)."""
+    g = torch.Generator(device=dev).manual_seed(seed)
+    rows = torch.empty((n_rows, 512), dtype=torch.float16, device=dev)
+    chunk = 1_000_000
+    for r0 in range(0, n_rows, chunk):
+        n = min(chunk, n_rows - r0)
+        x = torch.randn((n, 512), generator=g, device=dev)
+        rows[r0:r0 + n] = (x / x.norm(dim=-1, keepdim=True)).half()
+    return rows
+
+
+def time_steps(torch, fn, steps, warmup, world):
+    for _ in range(warmup):
+        fn()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier_sync(world)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    barrier_sync(world)
+    return e0.elapsed_time(e1)
+
+
+def bench_search(pkg, dev, rank, world, steps, warmup, total_rows, Q, k, peaks):
+    import torch
+    _lib = pkg._lib
+    D = 512
+    lo, hi = pkg.search.shard_bounds(total_rows, world, rank)
+    store = pkg.search.FrameStore(make_store(torch, dev, hi - lo, seed=2 + rank), row_offset=lo)
+    sharded = pkg.search.ShardedFrameStore(store) if world > 1 else store
+    g = torch.Generator(device="cpu").manual_seed(3)
+    qh = torch.randn((Q, D), generator=g)
+    qh = (qh / qh.norm(dim=-1, keepdim=True)).pin_memory()
+    q = qh.to(dev).half()
+    res = {}
+
+    def step():
+        res["out"] = sharded.search(q, k)
+
+    launches0 = _lib.launch_count()
+    ms = max_over_ranks(time_steps(torch, step, steps, warmup, world), dev, world)
+    launches = (_lib.launch_count() - launches0) * steps // (steps + warmup)
+    sc, idx = res["out"]
+    assert torch.all(sc[:, 1:] <= sc[:, :-1]) and int(idx.min()) >= 0 and int(idx.max()) < total_rows
+
+    # ---- end to end: pinned fp32 queries on the host -> H2D -> scan -> D2H of (scores, ids)
+    def step_e2e():
+        s, i = sharded.search(qh.to(dev, non_blocking=True), k)
+        res["host"] = (s.cpu(), i.cpu())
+
+    e2e_ms = max_over_ranks(time_steps(torch, step_e2e, steps, 2, world), dev, world)
+
+    n_local = hi - lo
+    flops = 2.0 * Q * n_local * D
+    nbytes = n_local * D * 2 + Q * D * 2 + Q * k * 12
+    out = {
+        "metric": SEARCH_METRIC if world == 1 else "queries/s top-100 over 100M-frame store row-sharded",
+        "unit": "queries/s", "value": round(Q * steps / (ms * 1e-3), 1), "ms_per_step": round(ms / steps, 3),
+        "steps": steps, "warmup": warmup, "gpu_launches": int(launches),
+        "scaling": "strong" if world > 1 else "weak",
+        "config": {"workload": f"cosine top-{k}, {Q} queries x {total_rows} frames x {D}-d fp16 store"
+                               + (f", row-sharded over {world} GPUs + NCCL all-gather + merge" if world > 1 else ""),
+                   "l2": "store (>= 10 GB per GPU) is far larger than L2"},
+        "e2e": {"value": round(Q * steps / (e2e_ms * 1e-3), 1), "unit": "queries/s",
+                "h2d_bytes_per_step": Q * D * 4, "d2h_bytes_per_step": Q * k * 12,
+                "api": "FrameStore.search(pinned fp32 queries) -> host (scores, ids)"},
+    }
+    if rank == 0:
+        # dominant kernel, timed live (separate pass): algorithmic FLOPs (and bytes) per launch / duration
+        _lib.profile_enable(True)
+        for _ in range(steps):
+            store.search(q, k)
+        torch.cuda.synchronize()
+        fam = _lib.profile_read()
+        _lib.profile_enable(False)
+        scan_ms = fam["topk_scan"][0] / max(fam["topk_scan"][1], 1)
+        t_tc, t_hbm = flops / (peaks["tf_sustained"] * 1e12), nbytes / (peaks["hbm_gbs"] * 1e9)
+        tensor_bound = t_tc >= t_hbm
+        ach_tf = flops / (scan_ms * 1e-3) / 1e12
+        ach_gb = nbytes / (scan_ms * 1e-3) / 1e9
+        out["roofline"] = {
+            "bound": "tensor" if tensor_bound else "hbm", "kernel": "topk_scan_kernel (tcgen05 GEMM + fused top-k)",
+            "achieved": round(ach_tf if tensor_bound else ach_gb, 1),
+            "peak": peaks["tf_sustained"] if tensor_bound else peaks["hbm_gbs"],
+            "unit": "TFLOP/s" if tensor_bound else "GB/s",
+            "frac": round((ach_tf / peaks["tf_sustained"]) if tensor_bound else (ach_gb / peaks["hbm_gbs"]), 4),
+            "traffic": None, "peak_source": peaks["source"], "avg_launch_ms": round(scan_ms, 4),
+            "achieved_gbs": round(ach_gb, 1), "achieved_tflops": round(ach_tf, 1),
+            "share_of_step": round(fam["topk_scan"][0] / sum(v[0] for v in fam.values()), 4),
+            "family_ms_per_step": {kk: round(v[0] / steps, 4) for kk, v in fam.items() if v[1]},
+            "timing": "CUDA events around every launch, separate pass of the same K steps",
+        }
+    # ---- HBM-bound regime: small query batches stream the whole local shard once per step
+    regime = []
+    for qs in (1, 8, 32, 128):
+        qq = q[:qs].contiguous()
+        t = max_over_ranks(time_steps(torch, lambda: sharded.search(qq, k), steps, 3, world), dev, world) / steps
+        b = n_local * D * 2 + qs * D * 2 + qs * k * 12
+        gbs = b / (t * 1e-3) / 1e9
+        regime.append({"Q": qs, "ms": round(t, 4), "queries_per_s": round(qs / (t * 1e-3), 1),
+                       "GB_per_s_per_gpu": round(gbs, 1), "frac_of_hbm_peak": round(gbs / peaks["hbm_gbs"], 4)})
+    out["hbm_regime"] = regime
+    return out
+
+
+# ----------------------------------------------------------------------------------------------- CPU legs (oracle)
+def cpu_encode(vo, n_batches, warm=1, batch=32):
+    """The reference's ingest loop (embedding_service.py:467-502: batches of 32, no_grad, .cpu().numpy(), final
+    L2 normalise) over its own fp32 CPU ViT, restated in oracle/vit_oracle.py.  Returns (frames/s, threads)."""
+    import numpy as np
+    import torch
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    visual = vo.build_visual(VIT_NAME, seed=1)
+    _, pix = vo.synthetic_frames(batch * (n_batches + warm), seed=0)
+    vo.encode_image(visual, pix[:batch * warm], batch=batch)
+    t0 = time.perf_counter()
+    e = vo.encode_image(visual, pix[batch * warm:], batch=batch)
+    dt = time.perf_counter() - t0
+    assert e.shape == (batch * n_batches, 512) and np.isfinite(e).all()
+    return batch * n_batches / dt, threads
+
+
+def cpu_search(so, n_rows, n_queries, k):
+    """The reference's scan (embedding_service.py:314-320: np.dot + full argsort per query, no query batching) over an
+    fp32 store of n_rows.  Returns queries/s at n_rows."""
+    import numpy as np
+    rng = np.random.default_rng(2)
+    emb = so.normalise_store(rng.standard_normal((n_rows, 512), dtype=np.float32))
+    q = rng.standard_normal((n_queries + 1, 512), dtype=np.float32)
+    q /= np.linalg.norm(q, axis=-1, keepdims=True)
+    so.search_top_frames(emb, q[:1], k)
+    t0 = time.perf_counter()
+    for j in range(1, n_queries + 1):
+        so.search_top_frames(emb, q[j:j + 1], k)
+    return n_queries / (time.perf_counter() - t0)
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path for the same metric/config on all host threads (rank 0 only)."""
+    rank, _, world = dist_env()
+    if rank != 0:
+        return
+    from oracle import search_oracle as so, vit_oracle as vo
+    import torch
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    visual = vo.build_visual(VIT_NAME, seed=1)
+    batch = 32  # the reference's own batch size (embedding_service.py:461)
+    _, pix = vo.synthetic_frames(batch, seed=0)
+    for _ in range(max(1, min(args.warmup, 2))):
+        vo.encode_image(visual, pix, batch=batch)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        vo.encode_image(visual, pix, batch=batch)
+    dt = time.perf_counter() - t0
+    fps = batch * args.steps / dt
+    sample_rows = 1_000_000
+    qps_1m = cpu_search(so, sample_rows, 4, args.k)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": round(fps, 2), "unit": "frames/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 2),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "ViT-B/32 keyframe encoding, synthetic 224x224 frames, random-init weights",
+                   "step": "one batch of 32 frames (the reference's batch size) on the host cores"},
+        "cpu_baseline": {"value": round(fps, 2), "unit": "frames/s", "cores": threads, "kind": "port",
+                         "sample": f"{args.steps} batches of 32 frames, oracle/vit_oracle.py (fp32 torch CPU restatement "
+                                   "of openai/CLIP encode_image; the reference's `clip` submodule is absent)"},
+        "e2e": {"value": round(fps, 2), "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "search": {"impl": "reference", "metric": SEARCH_METRIC, "unit": "queries/s",
+                   "value": round(qps_1m * sample_rows / 10_000_000, 3),
+                   "sample": f"4 queries, top-{args.k}, np.dot + full argsort over {sample_rows} fp32 rows "
+                             f"({qps_1m:.2f} q/s), scaled linearly to 10 M rows (favours the reference: argsort is "
+                             "N log N)", "cores": threads},
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------------------------- main
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="both", choices=["both", "encode", "search"])
+    ap.add_argument("--batch", type=int, default=256, help="frames per GPU per step (configs[1])")
+    ap.add_argument("--store-rows", type=int, default=0, help="total store rows (default 10M at N=1, 100M at N>1)")
+    ap.add_argument("--queries", type=int, default=10_000)
+    ap.add_argument("--k", type=int, default=100)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    if args.impl == "reference":
+        run_reference(args)
+        return
+
+    import torch
+    import torch.distributed as dist
+    rank, local_rank, world = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this package has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    import __graft_entry__ as ge
+    pkg = ge.load_package()
+    from oracle import search_oracle as so, vit_oracle as vo  # vo: weight init + synthetic frames; so: cpu_baseline
+    peaks = load_peaks()
+
+    line = {"metric": METRIC, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": f"ViT-B/32 keyframe encoding, batch {args.batch} synthetic 224x224 frames per GPU, "
+                                   "bf16 tensor cores, random-init weights (seeded)",
+                       "parallelism": f"dp{world}",
+                       "l2": "8 distinct resident uint8 batches (308 MB) rotate; weights+activations exceed L2"}}
+    if args.workload in ("both", "encode"):
+        r = bench_encode(pkg, vo, dev, rank, world, args.steps, args.warmup, args.batch, peaks)
+        line.update(value=round(r["value"], 1), ms_per_step=round(r["ms_per_step"], 4), e2e=r["e2e"],
+                    gpu_launches=r["gpu_launches"], clocks=r["clocks"], roofline=r["roofline"])
+    if args.workload in ("both", "search"):
+        total = args.store_rows or (10_000_000 if world == 1 else 100_000_000)
+        s_steps = max(3, min(args.steps, 10))
+        line["search"] = bench_search(pkg, dev, rank, world, s_steps, 3, total, args.queries, args.k, peaks)
+        if args.workload == "search":
+            s = line["search"]
+            line.update(metric=s["metric"], unit=s["unit"], value=s["value"], ms_per_step=s["ms_per_step"],
+                        steps=s["steps"], scaling=s["scaling"], dtype="f16", e2e=s["e2e"],
+                        gpu_launches=s["gpu_launches"], roofline=s.get("roofline"), config=s["config"])
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        fps, threads = cpu_encode(vo, n_batches=8)
+        qps = cpu_search(so, 1_000_000, 4, args.k)
+        line["cpu_baseline"] = {
+            "value": round(fps, 2), "unit": "frames/s", "cores": threads, "kind": "port",
+            "sample": "256 frames (8 batches of 32, the reference's batch size) through oracle/vit_oracle.py on the "
+                      "host cores; the reference's `clip` dependency is an absent submodule",
+            "search": {"value": round(qps / 10.0, 3), "unit": "queries/s",
+                       "sample": f"4 queries top-{args.k} over 1 M fp32 rows ({qps:.2f} q/s), scaled linearly to 10 M"}}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -30,6 +30,8 @@ SIGNATURES = {
     "evr_last_error": (ctypes.c_char_p, []),
     "evr_version": (c_int, []),
     "evr_launch_count": (c_int64, []),
+    "evr_profile_enable": (c_int, [c_int]),
+    "evr_profile_read": (c_int, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(c_int64), c_int]),
     "evr_store_prepare": (c_int, [c_void_p, c_int, c_int64, c_int, c_void_p, c_void_p]),
     "evr_topk_workspace_bytes": (c_int, [c_int64, c_int, c_int, c_int, ctypes.POINTER(c_size_t)]),
     "evr_topk_search": (c_int, [c_void_p, c_int64, c_int, c_int64, c_void_p, c_int, c_int, c_void_p, c_void_p,
@@ -55,6 +57,22 @@ def check(status, what):
 
 def launch_count():
     return int(lib.evr_launch_count())
+
+
+PROFILE_FAMILIES = ("gemm_tc", "attention", "layernorm", "vit_misc", "topk_scan", "topk_final", "store")
+
+
+def profile_enable(on):
+    check(lib.evr_profile_enable(1 if on else 0), "evr_profile_enable")
+
+
+def profile_read():
+    """-> {family: (total_ms, launches)} since profile_enable(True)."""
+    n = len(PROFILE_FAMILIES)
+    ms = (ctypes.c_double * n)()
+    cnt = (c_int64 * n)()
+    check(lib.evr_profile_read(ms, cnt, n), "evr_profile_read")
+    return {f: (ms[i], int(cnt[i])) for i, f in enumerate(PROFILE_FAMILIES)}
 
 
 def current_stream_ptr():

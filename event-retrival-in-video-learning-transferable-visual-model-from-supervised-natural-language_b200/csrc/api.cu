@@ -1,5 +1,6 @@
 // libevr.so: error string, version, launch counter, tensor-map encoding.
 #include <mutex>
+#include <vector>
 
 #include "../../include/evr.h"
 #include "common.cuh"
@@ -64,9 +65,63 @@ int sm_count() {
   return n;
 }
 
+// ---- per-family kernel timing ---------------------------------------------------------------------
+std::atomic<int> g_profile_on{0};
+struct ProfRec {
+  int family;
+  cudaEvent_t e0, e1;
+};
+static std::mutex g_prof_mu;
+static std::vector<ProfRec*> g_prof;
+
+void prof_begin(int family, cudaStream_t s, void** token) {
+  ProfRec* r = new ProfRec();
+  r->family = family;
+  if (cudaEventCreate(&r->e0) != cudaSuccess || cudaEventCreate(&r->e1) != cudaSuccess) {
+    delete r;
+    return;
+  }
+  cudaEventRecord(r->e0, s);
+  *token = r;
+}
+void prof_end(void* token, cudaStream_t s) {
+  ProfRec* r = static_cast<ProfRec*>(token);
+  cudaEventRecord(r->e1, s);
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  g_prof.push_back(r);
+}
+static void prof_clear() {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  for (ProfRec* r : g_prof) {
+    cudaEventDestroy(r->e0);
+    cudaEventDestroy(r->e1);
+    delete r;
+  }
+  g_prof.clear();
+}
+
 }  // namespace evr
 
 extern "C" {
+int evr_profile_enable(int on) {
+  evr::prof_clear();
+  evr::g_profile_on.store(on ? 1 : 0);
+  return 0;
+}
+int evr_profile_read(double* ms_by_family, int64_t* launches_by_family, int n) {
+  EVR_REQUIRE(ms_by_family && launches_by_family && n >= evr::PF_COUNT, "evr_profile_read: need %d slots",
+              (int)evr::PF_COUNT);
+  for (int i = 0; i < n; ++i) { ms_by_family[i] = 0.0; launches_by_family[i] = 0; }
+  std::lock_guard<std::mutex> lk(evr::g_prof_mu);
+  for (evr::ProfRec* r : evr::g_prof) {
+    EVR_CHECK_CUDA(cudaEventSynchronize(r->e1));
+    float ms = 0.f;
+    EVR_CHECK_CUDA(cudaEventElapsedTime(&ms, r->e0, r->e1));
+    ms_by_family[r->family] += ms;
+    launches_by_family[r->family] += 1;
+  }
+  return 0;
+}
 const char* evr_last_error(void) { return evr::g_err; }
 int evr_version(void) { return 100; }
 int64_t evr_launch_count(void) { return evr::g_launches.load(); }

@@ -50,4 +50,30 @@ int make_tmap_2d_16b(CUtensorMap* out, const void* base, uint64_t rows, uint64_t
 
 int sm_count();
 
+// Optional per-kernel-family timing (bench.py's roofline leg): when enabled through evr_profile_enable(1), every
+// launch site brackets its kernel with a pair of CUDA events on the launching stream.  Off by default (no cost).
+enum ProfFamily : int {
+  PF_GEMM = 0,      // gemm_tc_kernel (all epilogues)
+  PF_ATTN = 1,      // attention_kernel
+  PF_LN = 2,        // layernorm_kernel
+  PF_VIT_MISC = 3,  // im2col, cls rows, final normalise/cast
+  PF_SCAN = 4,      // topk_scan_kernel
+  PF_FINAL = 5,     // topk_final_kernel (select / merge)
+  PF_STORE = 6,     // store_prepare_kernel, rescore_kernel
+  PF_COUNT = 7
+};
+extern std::atomic<int> g_profile_on;
+void prof_begin(int family, cudaStream_t s, void** token);
+void prof_end(void* token, cudaStream_t s);
+struct ProfScope {
+  void* token = nullptr;
+  cudaStream_t s;
+  ProfScope(int family, cudaStream_t stream) : s(stream) {
+    if (g_profile_on.load(std::memory_order_relaxed)) prof_begin(family, stream, &token);
+  }
+  ~ProfScope() {
+    if (token) prof_end(token, s);
+  }
+};
+
 }  // namespace evr

@@ -16,6 +16,7 @@ static int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const GemmAr
     EVR_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
     attr_set = true;
   }
+  ProfScope ps(PF_GEMM, stream);
   kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(ta, tb, args);
   EVR_CHECK_LAUNCH();
   return 0;

@@ -496,6 +496,7 @@ static int launch_final(const float* scores, const IdxT* idx, int P, int q_strid
   int kp = 1;
   while (kp < k) kp <<= 1;
   const size_t smem = static_cast<size_t>(kp) * 16;
+  ProfScope ps(PF_FINAL, stream);
   topk_final_kernel<IdxT><<<Q, 256, smem, stream>>>(scores, idx, P, q_stride, k, row_offset, out_scores, out_idx);
   EVR_CHECK_LAUNCH();
   return 0;
@@ -512,6 +513,7 @@ extern "C" int evr_store_prepare(const void* src, int src_dtype, int64_t N, int 
   if (N <= 0) return 0;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const unsigned blocks = static_cast<unsigned>((N + 7) / 8);
+  ProfScope ps(PF_STORE, s);
   if (src_dtype == 0)
     store_prepare_kernel<float><<<blocks, 256, 0, s>>>(static_cast<const float*>(src), N, D, static_cast<__half*>(dst_fp16));
   else
@@ -549,6 +551,8 @@ extern "C" int evr_topk_search(const void* store, int64_t N, int D, int64_t row_
   if (int r = make_tmap_2d_16b(&tq, queries, Q, D, static_cast<uint64_t>(D) * 2, kScanQTile, false)) return r;
   if (int r = make_tmap_2d_16b(&ts, store, N, D, static_cast<uint64_t>(D) * 2, kScanRowTile, false)) return r;
   const int smem = kScanQTile * D * 2 + kScanStages * kScanStageBytes + 1024 + 256;
+  {
+  ProfScope ps(PF_SCAN, s);
   if (p.epl == 16) {
     auto kern = topk_scan_kernel<16>;
     static int cfg16 = 0;
@@ -565,6 +569,7 @@ extern "C" int evr_topk_search(const void* store, int64_t N, int D, int64_t row_
       cfg64 = smem;
     }
     kern<<<p.grid, kScanThreads, smem, s>>>(tq, ts, a);
+  }
   }
   EVR_CHECK_LAUNCH();
   return launch_final<int>(a.part_score, a.part_idx, p.num_slices, p.q_pad, Q, k, row_offset, out_scores, out_idx, s);

@@ -46,6 +46,7 @@ int launch_im2col(const void* pixels, int pix_dtype, int B, int S, int p, int Kp
   const int g = S / p, K = 3 * p * p;
   const size_t total = static_cast<size_t>(B) * g * g * (K / 2);
   const unsigned blocks = static_cast<unsigned>((total + 255) / 256);
+  ProfScope ps(PF_VIT_MISC, stream);
   im2col_kernel<<<blocks, 256, 0, stream>>>(pixels, pix_dtype, total, S, p, g, K, Kp, out);
   EVR_CHECK_LAUNCH();
   return 0;
@@ -59,6 +60,7 @@ __global__ void cls_rows_kernel(float* __restrict__ x, const float* __restrict__
 }
 
 int launch_cls_rows(float* x, const float* cls, const float* pos, int B, int L, int d, cudaStream_t stream) {
+  ProfScope ps(PF_VIT_MISC, stream);
   cls_rows_kernel<<<B, 256, 0, stream>>>(x, cls, pos, L, d);
   EVR_CHECK_LAUNCH();
   return 0;
@@ -119,6 +121,7 @@ int launch_layernorm(const float* in, size_t in_stride, void* out, size_t out_st
                      const float* gamma, const float* beta, int rows, int d, cudaStream_t stream) {
   EVR_REQUIRE(d == 768 || d == 1024, "layernorm: width %d unsupported (768 | 1024)", d);
   const int blocks = (rows + 7) / 8;
+  ProfScope ps(PF_LN, stream);
   if (d == 768) {
     if (out_bf16) layernorm_kernel<6, true><<<blocks, 256, 0, stream>>>(in, in_stride, out, out_stride, gamma, beta, rows);
     else layernorm_kernel<6, false><<<blocks, 256, 0, stream>>>(in, in_stride, out, out_stride, gamma, beta, rows);
@@ -286,6 +289,7 @@ int launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L,
                                         static_cast<int>(smem)));
     configured = smem;
   }
+  ProfScope ps(PF_ATTN, stream);
   attention_kernel<<<dim3(heads, B), 128, smem, stream>>>(qkv, out, L, d, 0.125f);
   EVR_CHECK_LAUNCH();
   return 0;
@@ -316,6 +320,7 @@ l2norm_cast_kernel(const float* __restrict__ in, void* __restrict__ out, int out
 
 int launch_l2norm_cast(const float* in, void* out, int out_dtype, int rows, int D, int normalise,
                        cudaStream_t stream) {
+  ProfScope ps(PF_VIT_MISC, stream);
   l2norm_cast_kernel<<<(rows + 7) / 8, 256, 0, stream>>>(in, out, out_dtype, rows, D, normalise);
   EVR_CHECK_LAUNCH();
   return 0;

@@ -86,8 +86,9 @@ class FrameStore:
         Q = q.shape[0]
         k_eff = min(int(k), self.N)
         if Q == 0 or k_eff <= 0:
-            return (torch.empty((Q, 0), dtype=torch.float32, device=self.device),
-                    torch.empty((Q, 0), dtype=torch.int64, device=self.device))
+            kk = max(k_eff, 0)
+            return (torch.empty((Q, kk), dtype=torch.float32, device=self.device),
+                    torch.empty((Q, kk), dtype=torch.int64, device=self.device))
         if k_eff > MAX_FUSED_K:
             return self._search_large_k(q, k_eff)
         out_s = torch.empty((Q, k_eff), dtype=torch.float32, device=self.device)

@@ -89,3 +89,55 @@ class VisionEncoder:
                                          0 if out_dtype == torch.float32 else 1, 1 if normalise else 0,
                                          current_stream_ptr()), "evr_vit_encode")
         return out
+
+    @torch.no_grad()
+    def encode_stream(self, host_batches, normalise=True, out_dtype=torch.float32):
+        """Pipelined host->host encode: for every host batch ([B,S,S,3] uint8 or [B,3,S,S] float, ideally pinned)
+        yields a host tensor [B, out_dim].  The H2D copy of batch i+1 runs on a side stream while batch i is in the
+        tower, and batch i is handed back once its embeddings have landed in pinned memory -- the device-side shape
+        of the loop at Backend/services/embedding_service.py:467-493 (stack -> .to(device) -> encode_image ->
+        .cpu().numpy()), without its per-batch stall."""
+        dev = self.device
+        with torch.cuda.device(dev):
+            comp = torch.cuda.current_stream(dev)
+            copy = self._copy_stream = getattr(self, "_copy_stream", None) or torch.cuda.Stream(device=dev)
+            stage = [None, None]
+            out_host = [None, None]
+            ev_in = [torch.cuda.Event(), torch.cuda.Event()]
+            ev_free = [None, None]
+            ev_out = [torch.cuda.Event(), torch.cuda.Event()]
+            pending = None
+            for i, hb in enumerate(host_batches):
+                slot = i & 1
+                if isinstance(hb, torch.Tensor) and hb.is_cuda:
+                    raise ValueError("encode_stream takes host batches; use encode() for device tensors")
+                hb = torch.as_tensor(hb)
+                B = hb.shape[0]
+                if hb.dtype != torch.uint8:
+                    hb = hb.to(torch.float32)
+                if stage[slot] is None or stage[slot].shape[0] < B or stage[slot].dtype != hb.dtype \
+                        or stage[slot].shape[1:] != hb.shape[1:]:
+                    stage[slot] = torch.empty((max(B, 1),) + tuple(hb.shape[1:]), dtype=hb.dtype, device=dev)
+                    ev_free[slot] = None
+                if out_host[slot] is None or out_host[slot].shape[0] < B or out_host[slot].dtype != out_dtype:
+                    out_host[slot] = torch.empty((max(B, 1), self.out_dim), dtype=out_dtype).pin_memory()
+                with torch.cuda.stream(copy):
+                    if ev_free[slot] is not None:
+                        copy.wait_event(ev_free[slot])  # the tower has finished reading this staging slot
+                    stage[slot][:B].copy_(hb, non_blocking=True)
+                    ev_in[slot].record(copy)
+                comp.wait_event(ev_in[slot])
+                emb = self.encode(stage[slot][:B], normalise=normalise, out_dtype=out_dtype)
+                ev_free[slot] = torch.cuda.Event()
+                ev_free[slot].record(comp)
+                if pending is not None:  # slot^1's embeddings: wait, hand back, then reuse its pinned buffer
+                    pslot, pB = pending
+                    ev_out[pslot].synchronize()
+                    yield out_host[pslot][:pB].clone()
+                out_host[slot][:B].copy_(emb, non_blocking=True)
+                ev_out[slot].record(comp)
+                pending = (slot, B)
+            if pending is not None:
+                pslot, pB = pending
+                ev_out[pslot].synchronize()
+                yield out_host[pslot][:pB].clone()

@@ -20,6 +20,13 @@ int evr_version(void);
 /* number of kernels launched by this library since load (bench.py's gpu_launches) */
 int64_t evr_launch_count(void);
 
+/* Per-kernel-family device timing for the roofline report (bench.py): evr_profile_enable(1) clears the records and
+ * makes every launch site bracket its kernel with CUDA events on the launching stream; evr_profile_read sums them.
+ * Families: 0 tcgen05 GEMM, 1 attention core, 2 LayerNorm, 3 other ViT kernels, 4 fused scan+top-k,
+ * 5 final select/merge, 6 store prepare / re-score.  n >= 7. */
+int evr_profile_enable(int on);
+int evr_profile_read(double* ms_by_family, int64_t* launches_by_family, int n);
+
 /* ---- store preparation -------------------------------------------------------------
  * replaces  embeddings / np.linalg.norm(embeddings, axis=-1, keepdims=True)
  *           Backend/services/embedding_service.py:210 (get_embeddings)

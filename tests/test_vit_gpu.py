@@ -1,0 +1,142 @@
+"""GPU parity of the hand-written CLIP vision tower (through the C ABI) against the fp32 CPU oracle
+(oracle/vit_oracle.py, restatement of openai/CLIP clip/model.py) and of its tcgen05 GEMM building block against a
+plain torch fp32 matmul.
+
+Tolerance (north_star): bf16 operands with fp32 accumulation, fp32 residual stream and LayerNorm statistics =>
+cosine(new, oracle fp32) >= 0.999 per embedding row; the GEMM itself must match an fp32 matmul of the same bf16
+operands to fp32 round-off (bf16 output: one bf16 ulp)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import vit_oracle as vo
+
+pytestmark = pytest.mark.gpu
+MIN_COS = 0.999
+
+
+def _gemm(pkg, A, W, bias, out, epi):
+    lib, ptr = pkg._lib.lib, pkg._lib.ptr
+    M, K = A.shape
+    N = W.shape[0]
+    pkg._lib.check(lib.evr_gemm_bf16(ptr(A), ptr(W), ptr(bias), ptr(out), M, N, K, epi, pkg._lib.current_stream_ptr()),
+                   "evr_gemm_bf16")
+    torch.cuda.synchronize()
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (1, 512, 768), (7, 512, 768), (200, 768, 768), (50, 2304, 768),
+                                   (1600, 3072, 768), (12800, 768, 3072), (12544, 768, 3072), (514, 1024, 640),
+                                   (12800, 2304, 768), (300, 32, 64), (129, 96, 128)])
+@pytest.mark.parametrize("epi", [0, 1, 2, 3])
+def test_gemm_epilogues(pkg, cuda, M, N, K, epi):
+    g = torch.Generator().manual_seed(M * 31 + N * 7 + K + epi)
+    A = (torch.randn(M, K, generator=g) * 0.5).to(cuda).bfloat16()
+    W = (torch.randn(N, K, generator=g) * 0.05).to(cuda).bfloat16()
+    bias = torch.randn(N, generator=g).to(cuda)
+    ref = A.float() @ W.float().t() + bias
+    if epi in (0, 1):
+        out = torch.full((M, N), float("nan"), dtype=torch.bfloat16, device=cuda)
+        if epi == 1:
+            ref = ref * torch.sigmoid(1.702 * ref)  # QuickGELU, clip/model.py
+        _gemm(pkg, A, W, bias, out, epi)
+        tol = 2.0 ** -8 * ref.abs().clamp(min=1.0) + 1e-3  # one bf16 ulp
+        assert torch.all((out.float() - ref).abs() <= tol)
+    elif epi == 2:
+        res = torch.randn(M, N, generator=g).to(cuda)
+        out = res.clone()
+        _gemm(pkg, A, W, bias, out, epi)
+        assert torch.allclose(out, ref + res, atol=2e-4, rtol=1e-5)
+    else:
+        out = torch.full((M, N), float("nan"), dtype=torch.float32, device=cuda)
+        _gemm(pkg, A, W, bias, out, epi)
+        assert torch.allclose(out, ref, atol=2e-4, rtol=1e-5)
+
+
+def test_gemm_without_bias(pkg, cuda):
+    g = torch.Generator().manual_seed(3)
+    A = torch.randn(64, 768, generator=g).to(cuda).bfloat16()
+    W = (torch.randn(512, 768, generator=g) * 0.03).to(cuda).bfloat16()
+    out = torch.empty((64, 512), dtype=torch.float32, device=cuda)
+    _gemm(pkg, A, W, None, out, 3)
+    assert torch.allclose(out, A.float() @ W.float().t(), atol=2e-4, rtol=1e-5)
+
+
+def test_gemm_rejects_bad_shapes(pkg, cuda):
+    A = torch.zeros((8, 100), dtype=torch.bfloat16, device=cuda)
+    W = torch.zeros((64, 100), dtype=torch.bfloat16, device=cuda)
+    out = torch.zeros((8, 64), dtype=torch.float32, device=cuda)
+    with pytest.raises(pkg._lib.EvrError, match="K="):
+        _gemm(pkg, A, W, None, out, 3)
+
+
+def _cos(a, b):
+    return (a * b).sum(-1) / np.linalg.norm(a, axis=-1) / np.linalg.norm(b, axis=-1)
+
+
+@pytest.fixture(scope="module")
+def b32():
+    visual = vo.build_visual("ViT-B/32", seed=1)
+    u8, pix = vo.synthetic_frames(37, seed=0)
+    ref = vo.encode_image(visual, pix, normalise=False)
+    return visual, u8, pix, ref
+
+
+def test_vit_b32_matches_oracle(pkg, cuda, b32):
+    visual, u8, pix, ref = b32
+    enc = pkg.vit.VisionEncoder.from_state_dict(visual.state_dict(), "ViT-B/32", device=cuda, max_batch=16)
+    out = enc.encode(pix.to(cuda)).cpu().numpy()  # 37 frames through max_batch 16: chunks of 16, 16, 5
+    assert out.shape == (37, 512)
+    cos = _cos(out, ref)
+    assert cos.min() >= MIN_COS, cos.min()
+    assert np.abs(out - ref).max() <= 0.02 * np.abs(ref).max()
+
+
+def test_vit_batch_invariance(pkg, cuda, b32):
+    visual, u8, pix, ref = b32
+    enc = pkg.vit.VisionEncoder.from_state_dict(visual.state_dict(), "ViT-B/32", device=cuda, max_batch=64)
+    whole = enc.encode(pix.to(cuda))
+    one = torch.cat([enc.encode(pix[i:i + 1].to(cuda)) for i in (0, 5, 36)])
+    assert torch.equal(whole[[0, 5, 36]], one)  # a frame's embedding does not depend on its batch
+
+
+def test_vit_uint8_frames_and_normalised_fp16_output(pkg, cuda, b32):
+    visual, u8, pix, ref = b32
+    enc = pkg.vit.VisionEncoder.from_state_dict(visual.state_dict(), "ViT-B/32", device=cuda, max_batch=64)
+    out = enc.encode(u8.to(cuda), normalise=True, out_dtype=torch.float16)  # ToTensor+Normalize fused on device
+    assert out.dtype == torch.float16
+    o = out.float().cpu().numpy()
+    assert np.allclose(np.linalg.norm(o, axis=-1), 1.0, atol=2e-3)
+    refn = ref / np.linalg.norm(ref, axis=-1, keepdims=True)  # embedding_service.py:502
+    assert _cos(o, refn).min() >= MIN_COS
+
+
+def test_vit_from_full_clip_state_dict_prefix(pkg, cuda, b32):
+    visual, u8, pix, ref = b32
+    sd = {"visual." + k: v for k, v in visual.state_dict().items()}
+    sd["logit_scale"] = torch.tensor(4.6052)
+    enc = pkg.vit.VisionEncoder.from_state_dict(sd, "ViT-B/32", device=cuda, max_batch=8, prefix="visual.")
+    out = enc.encode(pix[:3].to(cuda)).cpu().numpy()
+    assert _cos(out, ref[:3]).min() >= MIN_COS
+    with pytest.raises(KeyError):
+        pkg.vit.VisionEncoder.from_state_dict({}, "ViT-B/32", device=cuda)
+
+
+@pytest.mark.parametrize("name,n", [("ViT-L/14", 3), ("ViT-B/16", 3)])
+def test_other_geometries(pkg, cuda, name, n):
+    visual = vo.build_visual(name, seed=2)
+    u8, pix = vo.synthetic_frames(n, seed=4)
+    ref = vo.encode_image(visual, pix, normalise=False)
+    enc = pkg.vit.VisionEncoder.from_state_dict(visual.state_dict(), name, device=cuda, max_batch=2)
+    out = enc.encode(pix.to(cuda)).cpu().numpy()
+    assert out.shape == ref.shape
+    assert _cos(out, ref).min() >= MIN_COS
+
+
+def test_vit_argument_errors(pkg, cuda, b32):
+    visual = b32[0]
+    enc = pkg.vit.VisionEncoder.from_state_dict(visual.state_dict(), "ViT-B/32", device=cuda, max_batch=4)
+    with pytest.raises(ValueError):
+        enc.encode(torch.zeros((1, 3, 200, 200), device=cuda))
+    with pytest.raises(ValueError):
+        enc.encode(torch.zeros((1, 224, 224, 4), dtype=torch.uint8, device=cuda))
+    assert enc.encode(torch.zeros((0, 3, 224, 224), device=cuda)).shape == (0, 512)
