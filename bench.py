@@ -380,8 +380,10 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": round(fps, 2), "unit": "frames/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 2),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "ViT-B/32 keyframe encoding, synthetic 224x224 frames, random-init weights",
-                   "step": "one batch of 32 frames (the reference's batch size) on the host cores"},
+        "config": {"workload": f"ViT-B/32 keyframe encoding, batch {args.batch} synthetic 224x224 frames per GPU, "
+                               "bf16 tensor cores, random-init weights (seeded)",
+                   "step": "bounded sample: one batch of 32 frames (the reference's own batch size, "
+                           "embedding_service.py:461) in fp32 on the host cores"},
         "cpu_baseline": {"value": round(fps, 2), "unit": "frames/s", "cores": threads, "kind": "port",
                          "sample": f"{args.steps} batches of 32 frames, oracle/vit_oracle.py (fp32 torch CPU restatement "
                                    "of openai/CLIP encode_image; the reference's `clip` submodule is absent)"},
