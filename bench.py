@@ -292,7 +292,8 @@ def bench_search(pkg, dev, rank, world, steps, warmup, total_rows, Q, k, peaks):
         torch.cuda.synchronize()
         fam = _lib.profile_read()
         _lib.profile_enable(False)
-        scan_ms = fam["topk_scan"][0] / max(fam["topk_scan"][1], 1)
+        # a search call launches the scan kernel twice (sample pre-pass + full scan): time per call = family / steps
+        scan_ms = fam["topk_scan"][0] / steps
         t_tc, t_hbm = flops / (peaks["tf_sustained"] * 1e12), nbytes / (peaks["hbm_gbs"] * 1e9)
         tensor_bound = t_tc >= t_hbm
         ach_tf = flops / (scan_ms * 1e-3) / 1e12
@@ -304,7 +305,7 @@ def bench_search(pkg, dev, rank, world, steps, warmup, total_rows, Q, k, peaks):
             "unit": "TFLOP/s" if tensor_bound else "GB/s",
             "frac": round((ach_tf / peaks["tf_sustained"]) if tensor_bound else (ach_gb / peaks["hbm_gbs"]), 4),
             "traffic": None, "peak_source": peaks["source"], "avg_launch_ms": round(scan_ms, 4),
-            "achieved_gbs": round(ach_gb, 1), "achieved_tflops": round(ach_tf, 1),
+            "launches_per_step": fam["topk_scan"][1] // steps, "achieved_gbs": round(ach_gb, 1), "achieved_tflops": round(ach_tf, 1),
             "share_of_step": round(fam["topk_scan"][0] / sum(v[0] for v in fam.values()), 4),
             "family_ms_per_step": {kk: round(v[0] / steps, 4) for kk, v in fam.items() if v[1]},
             "timing": "CUDA events around every launch, separate pass of the same K steps",

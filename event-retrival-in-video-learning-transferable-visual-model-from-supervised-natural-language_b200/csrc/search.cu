@@ -73,6 +73,12 @@ __device__ __forceinline__ uint32_t key_to_float_bits(uint32_t key) {
 }
 constexpr uint32_t kNegInfBits = 0xFF800000u;
 
+__device__ __forceinline__ float fmax3(float a, float b, float c) {  // one FMNMX3 on sm_100
+  float d;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
+}
+
 // ============================================================================ fused scan + top-k
 constexpr int kScanQTile = 128;     // queries per tile  (UMMA M, TMEM lanes)
 constexpr int kScanRowTile = 128;   // store rows per tile (UMMA N, TMEM columns per stage)
@@ -80,6 +86,7 @@ constexpr int kScanStages = 6;      // smem ring depth, 16 KB per stage
 constexpr int kScanAccStages = 4;   // TMEM accumulator stages (4 x 128 = 512 columns)
 constexpr int kScanThreads = 192;
 constexpr int kScanStageBytes = kScanRowTile * 64 * 2;
+constexpr int kMaxFusedK = 1024;   // candidate lists of 32*EPL entries must hold k + one tile of admissions
 
 struct ScanArgs {
   int64_t N;           // store rows on this GPU
@@ -89,6 +96,8 @@ struct ScanArgs {
   int tiles_per_slice; // 128-row tiles per slice
   int q_pad;           // num_qt * 128
   int cap;             // candidate-list capacity per query (32 * EPL)
+  const float* init_thresh;  // per-query admission threshold from the sample pre-pass (nullptr: -inf)
+  int init_stride;     // elements between consecutive queries' thresholds
   int2* cand;          // [grid][128][cap]  (score bits, local row)
   float* part_score;   // [num_slices][q_pad][k]
   int* part_idx;       // [num_slices][q_pad][k]
@@ -254,7 +263,12 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       const int qt = item % args.num_qt, slice = item / args.num_qt;
       const int q0 = qt * kScanQTile + quad * 32;  // first query of this warp
       const bool q_valid = q0 + lane < args.Q;
-      float thresh = q_valid ? -INFINITY : INFINITY;
+      // Admission is `score >= thresh`.  Any lower bound on the query's global k-th best score is a valid
+      // threshold (at least k rows reach it): the sample pre-pass supplies one (init_thresh), and every local prune
+      // raises it to the k-th best of the rows this item has seen.  NaN never admits (padding lanes).
+      float thresh = q_valid ? (args.init_thresh ? __ldg(args.init_thresh + static_cast<size_t>(q0 + lane) * args.init_stride)
+                                                 : -INFINITY)
+                             : __int_as_float(0x7fc00000);
       int cnt = 0;
       const int64_t t0 = static_cast<int64_t>(slice) * args.tiles_per_slice;
       int64_t t1 = t0 + args.tiles_per_slice;
@@ -265,20 +279,31 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         const int row_base = static_cast<int>(t * kScanRowTile);
         const int rows_left = static_cast<int>(args.N - row_base);  // > 0
 #pragma unroll 1
-        for (int c = 0; c < kScanRowTile / 32; ++c) {
-          uint32_t v[32];
-          tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + as * kScanRowTile + c * 32, v);
+        for (int c = 0; c < kScanRowTile / 64; ++c) {
+          uint32_t v[2][32];
+          const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + as * kScanRowTile + c * 64;
+          tmem_ld_32x32(taddr, v[0]);
+          tmem_ld_32x32(taddr + 32, v[1]);
           tmem_ld_wait();
-          float mx = __uint_as_float(v[0]);
 #pragma unroll
-          for (int j = 1; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(v[j]));
-          if (mx > thresh) {  // rare once the threshold has settled
+          for (int h = 0; h < 2; ++h) {
+            float m4[4];
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const int r = c * 32 + j;
-              if (__uint_as_float(v[j]) > thresh && r < rows_left) {
-                __stcg(buf + cnt, make_int2(static_cast<int>(v[j]), row_base + r));
-                ++cnt;
+            for (int u = 0; u < 4; ++u) {
+              m4[u] = fmax3(__uint_as_float(v[h][8 * u]), __uint_as_float(v[h][8 * u + 1]), __uint_as_float(v[h][8 * u + 2]));
+              m4[u] = fmax3(m4[u], __uint_as_float(v[h][8 * u + 3]), __uint_as_float(v[h][8 * u + 4]));
+              m4[u] = fmax3(m4[u], __uint_as_float(v[h][8 * u + 5]), __uint_as_float(v[h][8 * u + 6]));
+              m4[u] = fmaxf(m4[u], __uint_as_float(v[h][8 * u + 7]));
+            }
+            const float mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+            if (mx >= thresh) {  // rare once the threshold has settled
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                const int r = c * 64 + h * 32 + j;
+                if (__uint_as_float(v[h][j]) >= thresh && r < rows_left) {
+                  __stcg(buf + cnt, make_int2(static_cast<int>(v[h][j]), row_base + r));
+                  ++cnt;
+                }
               }
             }
           }
@@ -442,17 +467,19 @@ rescore_kernel(const __half* __restrict__ store, int64_t N, int D, const __half*
 }
 
 // ============================================================================ host side
-struct ScanPlan {
+struct ScanCore {  // one launch of topk_scan_kernel over N rows
   int epl, cap, num_qt, q_pad, num_slices, tiles_per_slice, grid;
-  size_t cand_bytes, part_score_bytes, part_idx_bytes, total_bytes;
+  size_t cand_bytes, part_score_bytes, part_idx_bytes;
+};
+struct ScanPlan {
+  ScanCore main, pre;
+  int64_t n0;  // rows of the sample pre-pass (0: none)
+  size_t cand_bytes, part_score_bytes, part_idx_bytes, sample_score_bytes, sample_idx_bytes, total_bytes;
 };
 
-static int plan_scan(int64_t N, int D, int Q, int k, ScanPlan* p) {
-  EVR_REQUIRE(N >= 1 && N < (int64_t(1) << 31) - 256, "top-k scan: N=%lld out of range", (long long)N);
-  EVR_REQUIRE(D % 64 == 0 && D >= 64 && D <= 512, "top-k scan: D=%d must be a multiple of 64 in [64, 512]", D);
-  EVR_REQUIRE(Q >= 1, "top-k scan: Q=%d", Q);
-  EVR_REQUIRE(k >= 1 && k <= 512, "top-k scan: k=%d must be in [1, 512]", k);
-  const int sms = sm_count();
+static size_t up256(size_t x) { return (x + 255) & ~size_t(255); }
+
+static void plan_core(int64_t N, int Q, int k, int sms, ScanCore* p) {
   p->epl = k <= 128 ? 16 : 64;
   p->cap = 32 * p->epl;
   p->num_qt = (Q + kScanQTile - 1) / kScanQTile;
@@ -479,14 +506,39 @@ static int plan_scan(int64_t N, int D, int Q, int k, ScanPlan* p) {
   p->num_slices = static_cast<int>((tiles + p->tiles_per_slice - 1) / p->tiles_per_slice);
   const long long items = static_cast<long long>(p->num_qt) * p->num_slices;
   p->grid = static_cast<int>(items < sms ? items : sms);
-  p->cand_bytes = static_cast<size_t>(p->grid) * kScanQTile * p->cap * sizeof(int2);
-  p->part_score_bytes = static_cast<size_t>(p->num_slices) * p->q_pad * k * sizeof(float);
-  p->part_idx_bytes = static_cast<size_t>(p->num_slices) * p->q_pad * k * sizeof(int);
-  auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
-  p->cand_bytes = up(p->cand_bytes);
-  p->part_score_bytes = up(p->part_score_bytes);
-  p->part_idx_bytes = up(p->part_idx_bytes);
-  p->total_bytes = p->cand_bytes + p->part_score_bytes + p->part_idx_bytes + 256;
+  p->cand_bytes = up256(static_cast<size_t>(p->grid) * kScanQTile * p->cap * sizeof(int2));
+  p->part_score_bytes = up256(static_cast<size_t>(p->num_slices) * p->q_pad * k * sizeof(float));
+  p->part_idx_bytes = up256(static_cast<size_t>(p->num_slices) * p->q_pad * k * sizeof(int));
+}
+
+// Sample pre-pass: the exact top-k of the first n0 rows gives every query a lower bound on its global k-th best
+// score, so the main scan starts with a pass rate of ~k/n0 instead of admitting everything (and pruning) until its
+// own threshold settles.  n0 ~ the rows one SM sees at small query batch; < 1 % of the scan at any size.
+static int64_t sample_rows(int64_t N) {
+  if (N < 32768) return 0;
+  int64_t n0 = N / 8;
+  if (n0 > 65536) n0 = 65536;
+  return n0 & ~int64_t(kScanRowTile - 1);
+}
+
+static int plan_scan(int64_t N, int D, int Q, int k, ScanPlan* p) {
+  EVR_REQUIRE(N >= 1 && N < (int64_t(1) << 31) - 256, "top-k scan: N=%lld out of range", (long long)N);
+  EVR_REQUIRE(D % 64 == 0 && D >= 64 && D <= 512, "top-k scan: D=%d must be a multiple of 64 in [64, 512]", D);
+  EVR_REQUIRE(Q >= 1, "top-k scan: Q=%d", Q);
+  EVR_REQUIRE(k >= 1 && k <= kMaxFusedK, "top-k scan: k=%d must be in [1, %d]", k, kMaxFusedK);
+  const int sms = sm_count();
+  plan_core(N, Q, k, sms, &p->main);
+  p->n0 = sample_rows(N);
+  p->pre = ScanCore{};
+  if (p->n0 > 0) plan_core(p->n0, Q, k, sms, &p->pre);
+  auto mx = [](size_t a, size_t b) { return a > b ? a : b; };
+  p->cand_bytes = mx(p->main.cand_bytes, p->pre.cand_bytes);
+  p->part_score_bytes = mx(p->main.part_score_bytes, p->pre.part_score_bytes);
+  p->part_idx_bytes = mx(p->main.part_idx_bytes, p->pre.part_idx_bytes);
+  p->sample_score_bytes = p->n0 > 0 ? up256(static_cast<size_t>(Q) * k * sizeof(float)) : 0;
+  p->sample_idx_bytes = p->n0 > 0 ? up256(static_cast<size_t>(Q) * k * sizeof(int64_t)) : 0;
+  p->total_bytes = p->cand_bytes + p->part_score_bytes + p->part_idx_bytes + p->sample_score_bytes +
+                   p->sample_idx_bytes + 256;
   return 0;
 }
 
@@ -499,6 +551,19 @@ static int launch_final(const float* scores, const IdxT* idx, int P, int q_strid
   ProfScope ps(PF_FINAL, stream);
   topk_final_kernel<IdxT><<<Q, 256, smem, stream>>>(scores, idx, P, q_stride, k, row_offset, out_scores, out_idx);
   EVR_CHECK_LAUNCH();
+  return 0;
+}
+
+template <int EPL>
+static int launch_scan(int grid, int smem, cudaStream_t s, const CUtensorMap& tq, const CUtensorMap& ts,
+                       const ScanArgs& a) {
+  auto kern = topk_scan_kernel<EPL>;
+  static int configured = 0;  // per instantiation
+  if (smem > configured) {
+    EVR_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = smem;
+  }
+  kern<<<grid, kScanThreads, smem, s>>>(tq, ts, a);
   return 0;
 }
 
@@ -530,6 +595,31 @@ extern "C" int evr_topk_workspace_bytes(int64_t N, int D, int Q, int k, size_t* 
   return 0;
 }
 
+static int run_scan(const ScanCore& c, const void* store, int64_t N, int D, const void* queries, int Q, int k,
+                    const float* init_thresh, int init_stride, int2* cand, float* part_score, int* part_idx,
+                    cudaStream_t s) {
+  ScanArgs a{};
+  a.N = N; a.D = D; a.Q = Q; a.k = k;
+  a.num_qt = c.num_qt; a.num_slices = c.num_slices; a.tiles_per_slice = c.tiles_per_slice; a.q_pad = c.q_pad;
+  a.cap = c.cap;
+  a.init_thresh = init_thresh; a.init_stride = init_stride;
+  a.cand = cand; a.part_score = part_score; a.part_idx = part_idx;
+  CUtensorMap tq, ts;
+  if (int r = make_tmap_2d_16b(&tq, queries, Q, D, static_cast<uint64_t>(D) * 2, kScanQTile, false)) return r;
+  if (int r = make_tmap_2d_16b(&ts, store, N, D, static_cast<uint64_t>(D) * 2, kScanRowTile, false)) return r;
+  const int smem = kScanQTile * D * 2 + kScanStages * kScanStageBytes + 1024 + 256;
+  {
+    ProfScope ps(PF_SCAN, s);
+    if (c.epl == 16) {
+      if (int r = launch_scan<16>(c.grid, smem, s, tq, ts, a)) return r;
+    } else {
+      if (int r = launch_scan<64>(c.grid, smem, s, tq, ts, a)) return r;
+    }
+  }
+  EVR_CHECK_LAUNCH();
+  return 0;
+}
+
 extern "C" int evr_topk_search(const void* store, int64_t N, int D, int64_t row_offset, const void* queries, int Q,
                                int k, float* out_scores, int64_t* out_idx, void* workspace, size_t workspace_bytes,
                                void* stream) {
@@ -540,39 +630,23 @@ extern "C" int evr_topk_search(const void* store, int64_t N, int D, int64_t row_
               p.total_bytes);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   uint8_t* ws = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~uintptr_t(255));
-  ScanArgs a{};
-  a.N = N; a.D = D; a.Q = Q; a.k = k;
-  a.num_qt = p.num_qt; a.num_slices = p.num_slices; a.tiles_per_slice = p.tiles_per_slice; a.q_pad = p.q_pad;
-  a.cap = p.cap;
-  a.cand = reinterpret_cast<int2*>(ws);
-  a.part_score = reinterpret_cast<float*>(ws + p.cand_bytes);
-  a.part_idx = reinterpret_cast<int*>(ws + p.cand_bytes + p.part_score_bytes);
-  CUtensorMap tq, ts;
-  if (int r = make_tmap_2d_16b(&tq, queries, Q, D, static_cast<uint64_t>(D) * 2, kScanQTile, false)) return r;
-  if (int r = make_tmap_2d_16b(&ts, store, N, D, static_cast<uint64_t>(D) * 2, kScanRowTile, false)) return r;
-  const int smem = kScanQTile * D * 2 + kScanStages * kScanStageBytes + 1024 + 256;
-  {
-  ProfScope ps(PF_SCAN, s);
-  if (p.epl == 16) {
-    auto kern = topk_scan_kernel<16>;
-    static int cfg16 = 0;
-    if (smem > cfg16) {
-      EVR_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-      cfg16 = smem;
-    }
-    kern<<<p.grid, kScanThreads, smem, s>>>(tq, ts, a);
-  } else {
-    auto kern = topk_scan_kernel<64>;
-    static int cfg64 = 0;
-    if (smem > cfg64) {
-      EVR_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-      cfg64 = smem;
-    }
-    kern<<<p.grid, kScanThreads, smem, s>>>(tq, ts, a);
+  int2* cand = reinterpret_cast<int2*>(ws);
+  float* part_score = reinterpret_cast<float*>(ws + p.cand_bytes);
+  int* part_idx = reinterpret_cast<int*>(ws + p.cand_bytes + p.part_score_bytes);
+  float* sample_score = reinterpret_cast<float*>(ws + p.cand_bytes + p.part_score_bytes + p.part_idx_bytes);
+  int64_t* sample_idx = reinterpret_cast<int64_t*>(ws + p.cand_bytes + p.part_score_bytes + p.part_idx_bytes +
+                                                   p.sample_score_bytes);
+  const float* init = nullptr;
+  if (p.n0 > 0) {
+    if (int r = run_scan(p.pre, store, p.n0, D, queries, Q, k, nullptr, 0, cand, part_score, part_idx, s)) return r;
+    if (int r = launch_final<int>(part_score, part_idx, p.pre.num_slices, p.pre.q_pad, Q, k, 0, sample_score,
+                                  sample_idx, s))
+      return r;
+    init = sample_score + (k - 1);  // k-th best of the sample
   }
-  }
-  EVR_CHECK_LAUNCH();
-  return launch_final<int>(a.part_score, a.part_idx, p.num_slices, p.q_pad, Q, k, row_offset, out_scores, out_idx, s);
+  if (int r = run_scan(p.main, store, N, D, queries, Q, k, init, k, cand, part_score, part_idx, s)) return r;
+  return launch_final<int>(part_score, part_idx, p.main.num_slices, p.main.q_pad, Q, k, row_offset, out_scores,
+                           out_idx, s);
 }
 
 extern "C" int evr_topk_merge(const float* scores, const int64_t* idx, int P, int Q, int k, float* out_scores,

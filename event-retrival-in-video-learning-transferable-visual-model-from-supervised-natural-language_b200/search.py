@@ -15,7 +15,7 @@ import torch
 from . import _lib
 from ._lib import lib, check, ptr, current_stream_ptr
 
-MAX_FUSED_K = 512
+MAX_FUSED_K = 1024
 
 
 def _as_query_tensor(queries, device, D):
@@ -100,21 +100,8 @@ class FrameStore:
         return out_s, out_i
 
     def _search_large_k(self, q, k):
-        """k > 512: scan row chunks of <= 512*... with the fused kernel (k=512 each) and merge on-device."""
-        # Every chunk of C rows contributes its top-min(512, C); choosing C <= 512 makes that exact.
-        C = MAX_FUSED_K
-        parts_s, parts_i = [], []
-        for r0 in range(0, self.N, C):
-            sub = FrameStore(self.rows[r0:r0 + C], self.row_offset + r0)
-            s, i = sub.search(q, C)
-            if s.shape[1] < C:
-                pad = C - s.shape[1]
-                s = torch.cat([s, torch.full((s.shape[0], pad), float("-inf"), device=s.device)], 1)
-                i = torch.cat([i, torch.full((i.shape[0], pad), -1, dtype=torch.int64, device=i.device)], 1)
-            parts_s.append(s)
-            parts_i.append(i)
-        # iterative on-device merge, 1024-wide lists at most
-        raise NotImplementedError("k > 512 is served by FrameStore.search_all_sorted")
+        raise ValueError(f"top_k={k} exceeds the fused kernel's limit of {MAX_FUSED_K} (the reference UI asks for "
+                         "top_k*3 <= 300); split the request or lower top_k")
 
     def rescore(self, query, rows):
         """cosine of `query` [D] with the given local rows -> fp32 [R] (embedding_service.py:274-279)."""

@@ -42,7 +42,10 @@ int evr_store_prepare(const void* src, int src_dtype, int64_t N, int D, void* ds
  * store   [N, D] fp16 (from evr_store_prepare), D % 64 == 0, D <= 512
  * queries [Q, D] fp16
  * out_scores [Q, k] fp32 descending; out_idx [Q, k] int64 = row_offset + local row.
- * If k > N the tail is filled with score -inf / idx -1.
+ * 1 <= k <= 1024.  If k > N the tail is filled with score -inf / idx -1.
+ * For N >= 32768 the call first runs the same kernel over a sample of min(N/8, 65536) rows; the sample's k-th
+ * best score per query is the admission threshold the full scan starts from (results are unchanged: it is a lower
+ * bound on the global k-th best).
  * workspace: evr_topk_workspace_bytes(N, D, Q, k) bytes of device memory. */
 int evr_topk_workspace_bytes(int64_t N, int D, int Q, int k, size_t* out_bytes);
 int evr_topk_search(const void* store, int64_t N, int D, int64_t row_offset, const void* queries, int Q, int k,
