@@ -9,7 +9,7 @@ namespace evr {
 template <int BLOCK_N, int EPI>
 static int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const GemmArgs& args, int grid,
                       cudaStream_t stream) {
-  using Cfg = GemmCfg<BLOCK_N>;
+  using Cfg = GemmCfg<BLOCK_N, EPI>;
   auto kern = gemm_tc_kernel<BLOCK_N, EPI>;
   static bool attr_set = false;  // per instantiation
   if (!attr_set) {

@@ -38,26 +38,42 @@ constexpr int kGemmBlockM = 128;
 constexpr int kGemmBlockK = 64;  // 64 x 16-bit = one 128-B swizzle atom row
 constexpr int kGemmThreads = 256;
 
-template <int BLOCK_N>
+// Epilogue staging: every epilogue warp owns a [32 rows x 64 columns] tile in shared memory (row pitch padded by 16 B
+// so the row-per-lane writes are bank-conflict free).  TMEM hands each lane one accumulator ROW; staging turns that
+// into row-contiguous, fully coalesced 16-B global accesses (4 or 2 whole rows of 128/256 B per warp instruction).
+constexpr int kEpiCols = 64;
+template <int EPI>
+struct EpiCfg {
+  static constexpr bool kOutBf16 = (EPI == 0 || EPI == 1);
+  static constexpr int kElt = kOutBf16 ? 2 : 4;
+  static constexpr int kRowBytes = kEpiCols * kElt;       // 128 | 256
+  static constexpr int kPitch = kRowBytes + 16;           // 144 | 272
+  static constexpr int kWarpBytes = 32 * kPitch;
+  static constexpr int kBytes = 4 * kWarpBytes;           // 18 432 | 34 816
+  static constexpr int kUnitsPerRow = kRowBytes / 16;     // 8 | 16
+};
+
+template <int BLOCK_N, int EPI>
 struct GemmCfg {
   static constexpr int kABytes = kGemmBlockM * kGemmBlockK * 2;
   static constexpr int kBBytes = BLOCK_N * kGemmBlockK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages = (200 * 1024) / kStageBytes;
+  static constexpr int kEpiBytes = EpiCfg<EPI>::kBytes;
+  static constexpr int kStages = (227 * 1024 - 1024 - 256 - kEpiBytes) / kStageBytes;
   static constexpr int kTmemCols = (2 * BLOCK_N <= 32)    ? 32
                                    : (2 * BLOCK_N <= 64)  ? 64
                                    : (2 * BLOCK_N <= 128) ? 128
                                    : (2 * BLOCK_N <= 256) ? 256
                                                           : 512;
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kEpiBytes + 1024 /*align slack*/ + 256 /*barriers*/;
   static_assert(BLOCK_N % 16 == 0 && BLOCK_N >= 32 && BLOCK_N <= 256, "invalid UMMA N");
   static_assert(kBBytes % 1024 == 0, "B stage must keep 1024-B alignment for SWIZZLE_128B");
   static_assert(kStages >= 3, "pipeline too shallow");
 };
 
 __device__ __forceinline__ float quick_gelu(float x) {
-  // clip/model.py QuickGELU: x * sigmoid(1.702 x)
-  return x * __frcp_rn(1.0f + __expf(-1.702f * x));
+  // clip/model.py QuickGELU: x * sigmoid(1.702 x)   (MUFU.EX2 + MUFU.RCP; the IEEE reciprocal costs 3x the epilogue)
+  return __fdividef(x, 1.0f + __expf(-1.702f * x));
 }
 
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
@@ -69,11 +85,13 @@ template <int BLOCK_N, int EPI>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const GemmArgs args) {
-  using Cfg = GemmCfg<BLOCK_N>;
+  using Cfg = GemmCfg<BLOCK_N, EPI>;
+  using Epi = EpiCfg<EPI>;
   constexpr int kStages = Cfg::kStages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
+  uint8_t* smem_epi = smem + kStages * Cfg::kStageBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_epi + Cfg::kEpiBytes);
   uint64_t* full_bar = bars;                     // [kStages]  TMA -> MMA
   uint64_t* empty_bar = bars + kStages;          // [kStages]  MMA -> TMA
   uint64_t* tmem_full = bars + 2 * kStages;      // [2]        MMA -> epilogue
@@ -158,48 +176,46 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       }
     }
   } else if (warp >= 4) {
-    // ===== epilogue: warp q owns TMEM lanes [32q, 32q+32) =====
+    // ===== epilogue: warp q owns TMEM lanes [32q, 32q+32) = rows [32q, 32q+32) of the tile =====
     const int q = warp - 4;
+    uint8_t* stage = smem_epi + q * Epi::kWarpBytes;
+    uint8_t* my_row = stage + lane * Epi::kPitch;
     int as = 0;
     uint32_t aphase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int m_idx = tile % num_m, n_idx = tile / num_m;
       mbar_wait(&tmem_full[as], aphase);
       tc_fence_after();
-      const int row = m_idx * kGemmBlockM + q * 32 + lane;
-      const bool row_ok = row < args.M;
-      size_t out_row = row;
-      const float* pos_row = nullptr;
-      if constexpr (EPI == EPI_PATCH) {
-        const int b = row / args.patches, p = row - b * args.patches;
-        out_row = static_cast<size_t>(b) * (args.patches + 1) + 1 + p;
-        pos_row = args.pos + static_cast<size_t>(1 + p) * args.N;
-      }
+      const int row0 = m_idx * kGemmBlockM + q * 32;  // first row of this warp
 #pragma unroll 1
-      for (int c = 0; c < BLOCK_N / 32; ++c) {
-        const int col0 = n_idx * BLOCK_N + c * 32;
+      for (int c = 0; c < BLOCK_N / kEpiCols; ++c) {
+        const int col0 = n_idx * BLOCK_N + c * kEpiCols;
         if (col0 >= args.N) break;  // warp-uniform
-        uint32_t v[32];
-        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BLOCK_N + c * 32, v);
+        // ---- accumulator row of this lane: 64 columns, + bias (+ QuickGELU), into the staging tile
+        uint32_t v[2][32];
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BLOCK_N + c * kEpiCols;
+        tmem_ld_32x32(taddr, v[0]);
+        tmem_ld_32x32(taddr + 32, v[1]);
         tmem_ld_wait();
-        float f[32];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
-        if (args.bias != nullptr) {
-          const float4* b4 = reinterpret_cast<const float4*>(args.bias + col0);
+        for (int h = 0; h < 2; ++h) {
+          float f[32];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float4 b = __ldg(b4 + j);
-            f[4 * j] += b.x; f[4 * j + 1] += b.y; f[4 * j + 2] += b.z; f[4 * j + 3] += b.w;
-          }
-        }
-        if (row_ok) {
-          if constexpr (EPI == EPI_BF16 || EPI == EPI_BF16_GELU) {
-            if constexpr (EPI == EPI_BF16_GELU) {
+          for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[h][j]);
+          if (args.bias != nullptr && col0 + h * 32 < args.N) {
+            const float4* b4 = reinterpret_cast<const float4*>(args.bias + col0 + h * 32);
 #pragma unroll
-              for (int j = 0; j < 32; ++j) f[j] = quick_gelu(f[j]);
+            for (int j = 0; j < 8; ++j) {
+              const float4 bb = __ldg(b4 + j);
+              f[4 * j] += bb.x; f[4 * j + 1] += bb.y; f[4 * j + 2] += bb.z; f[4 * j + 3] += bb.w;
             }
-            uint4* o = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(args.out) + out_row * args.ldo + col0);
+          }
+          if constexpr (EPI == EPI_BF16_GELU) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = quick_gelu(f[j]);
+          }
+          if constexpr (Epi::kOutBf16) {
+            uint4* o = reinterpret_cast<uint4*>(my_row + h * 64);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
               uint4 w;
@@ -210,26 +226,43 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
               o[j] = w;
             }
           } else {
-            float4* o = reinterpret_cast<float4*>(static_cast<float*>(args.out) + out_row * args.ldo + col0);
-            if constexpr (EPI == EPI_F32_RESID) {
-#pragma unroll
-              for (int j = 0; j < 8; ++j) {
-                const float4 r = o[j];
-                f[4 * j] += r.x; f[4 * j + 1] += r.y; f[4 * j + 2] += r.z; f[4 * j + 3] += r.w;
-              }
-            }
-            if constexpr (EPI == EPI_PATCH) {
-              const float4* p4 = reinterpret_cast<const float4*>(pos_row + col0);
-#pragma unroll
-              for (int j = 0; j < 8; ++j) {
-                const float4 r = __ldg(p4 + j);
-                f[4 * j] += r.x; f[4 * j + 1] += r.y; f[4 * j + 2] += r.z; f[4 * j + 3] += r.w;
-              }
-            }
+            float4* o = reinterpret_cast<float4*>(my_row + h * 128);
 #pragma unroll
             for (int j = 0; j < 8; ++j) o[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
           }
         }
+        __syncwarp();
+        // ---- coalesced copy-out: 16-B units, consecutive lanes walk along a row
+        constexpr int kUnits = 32 * Epi::kUnitsPerRow;
+        constexpr int kColsPerUnit = 16 / Epi::kElt;
+#pragma unroll
+        for (int it = 0; it < kUnits / 32; ++it) {
+          const int u = it * 32 + lane;
+          const int r = u / Epi::kUnitsPerRow, cu = u % Epi::kUnitsPerRow;
+          const int row = row0 + r, col = col0 + cu * kColsPerUnit;
+          if (row < args.M && col < args.N) {
+            const uint4 sv = *reinterpret_cast<const uint4*>(stage + r * Epi::kPitch + cu * 16);
+            if constexpr (Epi::kOutBf16) {
+              *reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(args.out) + static_cast<size_t>(row) * args.ldo + col) = sv;
+            } else {
+              float4 x = *reinterpret_cast<const float4*>(&sv);
+              size_t out_row = row;
+              if constexpr (EPI == EPI_PATCH) {
+                const int bimg = row / args.patches, pp = row - bimg * args.patches;
+                out_row = static_cast<size_t>(bimg) * (args.patches + 1) + 1 + pp;
+                const float4 pe = __ldg(reinterpret_cast<const float4*>(args.pos + static_cast<size_t>(1 + pp) * args.N + col));
+                x.x += pe.x; x.y += pe.y; x.z += pe.z; x.w += pe.w;
+              }
+              float4* o = reinterpret_cast<float4*>(static_cast<float*>(args.out) + out_row * args.ldo + col);
+              if constexpr (EPI == EPI_F32_RESID) {
+                const float4 old = *o;
+                x.x += old.x; x.y += old.y; x.z += old.z; x.w += old.w;
+              }
+              *o = x;
+            }
+          }
+        }
+        __syncwarp();  // the staging tile is rewritten by the next chunk
       }
       tc_fence_before();
       __syncwarp();

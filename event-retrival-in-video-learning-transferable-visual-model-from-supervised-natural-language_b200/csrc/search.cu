@@ -5,7 +5,7 @@
 //   :210       embeddings / np.linalg.norm(embeddings, axis=-1, keepdims=True)     -> store_prepare
 //   :314 :365  similarities = np.dot(embeddings, q.T).flatten()                    -> topk_scan_kernel (MMA)
 //   :317-320   np.argsort(similarities)[::-1][:top_k]                              -> topk_scan_kernel epilogue
-//                                                                                     + topk_final_kernel
+//                                                                                     + topk_select_kernel
 //   :274-279   np.dot(embeddings[index:index+1], q.T)[0][0]                        -> rescore_kernel
 //
 // Scan kernel (one persistent CTA per SM, 192 threads):
@@ -89,18 +89,18 @@ constexpr int kScanStageBytes = kScanRowTile * 64 * 2;
 constexpr int kMaxFusedK = 1024;   // candidate lists of 32*EPL entries must hold k + one tile of admissions
 
 struct ScanArgs {
-  int64_t N;           // store rows on this GPU
+  int64_t N;           // store rows scanned by this launch
   int D, Q, k;
   int num_qt;          // query tiles
   int num_slices;      // store slices
   int tiles_per_slice; // 128-row tiles per slice
   int q_pad;           // num_qt * 128
-  int cap;             // candidate-list capacity per query (32 * EPL)
-  const float* init_thresh;  // per-query admission threshold from the sample pre-pass (nullptr: -inf)
-  int init_stride;     // elements between consecutive queries' thresholds
-  int2* cand;          // [grid][128][cap]  (score bits, local row)
-  float* part_score;   // [num_slices][q_pad][k]
-  int* part_idx;       // [num_slices][q_pad][k]
+  int cap;             // candidate-list capacity per (slice, query) = 32 * EPL
+  const float* init_thresh;  // per-query admission threshold from the sample pass (nullptr: -inf)
+  int2* lists;         // [num_slices][q_pad][cap]  (score bits, local row): candidates of one (slice, query)
+  int* counts;         // [num_slices][q_pad]       entries used in each list
+  float* group_max;    // sample pass only (else nullptr): [q_pad][groups] max score of every 64-row group
+  int groups;          // 64-row groups in the sample = N / 64
 };
 
 // Warp-cooperative exact prune of one query's candidate list to its top-k.  All 32 lanes call with the
@@ -257,17 +257,17 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     const int trigger = cap - kScanRowTile;
     int as = 0;
     uint32_t aphase = 0;
-    int2* const cand_warp = args.cand + (static_cast<size_t>(blockIdx.x) * kScanQTile + quad * 32) * cap;
-    int2* const buf = cand_warp + static_cast<size_t>(lane) * cap;
     for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
       const int qt = item % args.num_qt, slice = item / args.num_qt;
       const int q0 = qt * kScanQTile + quad * 32;  // first query of this warp
       const bool q_valid = q0 + lane < args.Q;
+      // the candidate list of (slice, query) is filled in place; the final select kernel reads it with its count
+      int2* const cand_warp = args.lists + (static_cast<size_t>(slice) * args.q_pad + q0) * cap;
+      int2* const buf = cand_warp + static_cast<size_t>(lane) * cap;
       // Admission is `score >= thresh`.  Any lower bound on the query's global k-th best score is a valid
       // threshold (at least k rows reach it): the sample pre-pass supplies one (init_thresh), and every local prune
       // raises it to the k-th best of the rows this item has seen.  NaN never admits (padding lanes).
-      float thresh = q_valid ? (args.init_thresh ? __ldg(args.init_thresh + static_cast<size_t>(q0 + lane) * args.init_stride)
-                                                 : -INFINITY)
+      float thresh = q_valid ? (args.init_thresh ? __ldg(args.init_thresh + q0 + lane) : -INFINITY)
                              : __int_as_float(0x7fc00000);
       int cnt = 0;
       const int64_t t0 = static_cast<int64_t>(slice) * args.tiles_per_slice;
@@ -285,6 +285,7 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           tmem_ld_32x32(taddr, v[0]);
           tmem_ld_32x32(taddr + 32, v[1]);
           tmem_ld_wait();
+          float gmx = -INFINITY;
 #pragma unroll
           for (int h = 0; h < 2; ++h) {
             float m4[4];
@@ -296,7 +297,8 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
               m4[u] = fmaxf(m4[u], __uint_as_float(v[h][8 * u + 7]));
             }
             const float mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
-            if (mx >= thresh) {  // rare once the threshold has settled
+            gmx = fmaxf(gmx, mx);
+            if (args.group_max == nullptr && mx >= thresh) {  // rare once the threshold has settled
 #pragma unroll
               for (int j = 0; j < 32; ++j) {
                 const int r = c * 64 + h * 32 + j;
@@ -307,6 +309,8 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
               }
             }
           }
+          if (args.group_max != nullptr && q_valid)  // sample pass: N is a multiple of the tile, no padding rows
+            args.group_max[static_cast<size_t>(q0 + lane) * args.groups + (t * (kScanRowTile / 64) + c)] = gmx;
         }
         tc_fence_before();
         __syncwarp();
@@ -325,26 +329,8 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           }
         }
       }
-      // ---- item done: exact top-k of every query of this warp -> partial lists
-      __syncwarp();
-      for (int src = 0; src < 32; ++src) {
-        const int q = q0 + src;
-        if (q >= args.Q) break;  // warp-uniform
-        int c_src = __shfl_sync(0xffffffffu, cnt, src);
-        int2* b_src = cand_warp + static_cast<size_t>(src) * cap;
-        if (c_src > k) {
-          warp_prune<EPL>(b_src, c_src, k, lane);
-          c_src = k;
-        }
-        const size_t o = (static_cast<size_t>(slice) * args.q_pad + q) * k;
-        for (int j = lane; j < k; j += 32) {
-          int2 e = make_int2(static_cast<int>(kNegInfBits), -1);
-          if (j < c_src) e = __ldcg(b_src + j);
-          args.part_score[o + j] = __int_as_float(e.x);
-          args.part_idx[o + j] = e.y;
-        }
-      }
-      __syncwarp();
+      // ---- item done: the list stays where it is; publish its length
+      if (q_valid && args.counts != nullptr) args.counts[static_cast<size_t>(slice) * args.q_pad + q0 + lane] = cnt;
     }
   }
 
@@ -356,7 +342,149 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   }
 }
 
-// ============================================================================ final select / merge
+// ============================================================================ sample threshold
+// k-th largest of a query's 64-row group maxima: k distinct rows score at least that much, so it is a lower bound
+// on the query's global k-th best score (the admission threshold of the full scan).  One warp per query.
+__global__ void __launch_bounds__(256)
+sample_kth_kernel(const float* __restrict__ group_max, int groups, int Q, int k, float* __restrict__ thresh) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int q = blockIdx.x * 8 + warp;
+  if (q >= Q) return;
+  const float* g = group_max + static_cast<size_t>(q) * groups;
+  uint32_t T = 0;
+#pragma unroll 1
+  for (int bit = 31; bit >= 0; --bit) {
+    const uint32_t c = T | (1u << bit);
+    int n = 0;
+    for (int i = lane; i < groups; i += 32) n += float_to_key(__float_as_uint(g[i])) >= c;  // L1-resident after pass 1
+    n = __reduce_add_sync(0xffffffffu, n);
+    if (n >= k) T = c;
+  }
+  if (lane == 0) thresh[q] = __uint_as_float(key_to_float_bits(T));
+}
+
+// ============================================================================ final select
+// One CTA per query: exact top-k of the candidates its slices admitted (lists[slice][q][0..counts)), sorted by
+// (score desc, row asc).  Candidates are gathered once into shared memory as 64-bit keys
+// (score key << 32 | ~row); an 8-pass MSB radix select finds the k-th key, the k winners are bitonic-sorted.
+// If a query has more candidates than fit (adversarial ties), the passes re-read the lists from global memory.
+struct SelectArgs {
+  const int2* lists;
+  const int* counts;
+  int P, q_pad, cap, k, smem_cap;
+  int64_t row_offset;
+  float* out_scores;
+  int64_t* out_idx;
+};
+
+__global__ void __launch_bounds__(256)
+topk_select_kernel(const SelectArgs a) {
+  extern __shared__ __align__(16) uint8_t ssm[];
+  __shared__ unsigned hist[256];
+  __shared__ int s_off[257];
+  __shared__ unsigned long long s_prefix;
+  __shared__ int s_remaining, s_count;
+  const int q = blockIdx.x, tid = threadIdx.x;
+  int kp = 1;
+  while (kp < a.k) kp <<= 1;
+  unsigned long long* win = reinterpret_cast<unsigned long long*>(ssm);  // [kp] winners
+  unsigned long long* keys = win + kp;                                   // [smem_cap] gathered candidates
+
+  // slice offsets (P <= 256)
+  if (tid < a.P) s_off[tid + 1] = a.counts[static_cast<size_t>(tid) * a.q_pad + q];
+  if (tid == 0) s_off[0] = 0;
+  __syncthreads();
+  if (tid == 0) {
+    int acc = 0;
+    for (int i = 1; i <= a.P; ++i) { acc += s_off[i]; s_off[i] = acc; }
+    s_prefix = 0ull; s_remaining = a.k; s_count = 0;
+  }
+  __syncthreads();
+  const int total = s_off[a.P];
+  const bool in_smem = total <= a.smem_cap;
+  auto make_key = [](int2 e) -> unsigned long long {
+    return (static_cast<unsigned long long>(float_to_key(static_cast<uint32_t>(e.x))) << 32) |
+           static_cast<uint32_t>(~static_cast<uint32_t>(e.y));
+  };
+  const int warp = tid >> 5, lane = tid & 31;
+  if (in_smem) {
+    for (int sl = warp; sl < a.P; sl += 8) {
+      const int o = s_off[sl], c = s_off[sl + 1] - o;
+      const int2* src = a.lists + (static_cast<size_t>(sl) * a.q_pad + q) * a.cap;
+      for (int j = lane; j < c; j += 32) keys[o + j] = make_key(__ldcg(src + j));
+    }
+  }
+  __syncthreads();
+  // visit every candidate key
+  auto for_each = [&](auto&& f) {
+    if (in_smem) {
+      for (int i = tid; i < total; i += 256) f(keys[i]);
+    } else {
+      for (int sl = warp; sl < a.P; sl += 8) {
+        const int c = s_off[sl + 1] - s_off[sl];
+        const int2* src = a.lists + (static_cast<size_t>(sl) * a.q_pad + q) * a.cap;
+        for (int j = lane; j < c; j += 32) f(make_key(__ldcg(src + j)));
+      }
+    }
+  };
+  for (int i = tid; i < kp; i += 256) win[i] = 0ull;  // key 0 sorts last: score -inf / row -1 padding
+  unsigned long long T = 0ull;
+  if (total > a.k) {
+    unsigned long long himask = 0ull;
+    for (int shift = 56; shift >= 0; shift -= 8) {
+      hist[tid] = 0;
+      __syncthreads();
+      const unsigned long long prefix = s_prefix;
+      for_each([&](unsigned long long key) {
+        if ((key & himask) == prefix) atomicAdd(&hist[(key >> shift) & 255ull], 1u);
+      });
+      __syncthreads();
+      if (tid == 0) {
+        int rem = s_remaining, acc = 0, b = 255;
+        for (; b > 0; --b) {
+          if (acc + static_cast<int>(hist[b]) >= rem) break;
+          acc += hist[b];
+        }
+        s_remaining = rem - acc;
+        s_prefix = prefix | (static_cast<unsigned long long>(b) << shift);
+      }
+      himask |= 255ull << shift;
+      __syncthreads();
+    }
+    T = s_prefix;  // k-th largest key (keys are unique: the row id is part of the key)
+  }
+  __syncthreads();
+  for_each([&](unsigned long long key) {
+    if (key >= T) {
+      const int pos = atomicAdd(&s_count, 1);
+      if (pos < kp) win[pos] = key;
+    }
+  });
+  __syncthreads();
+  for (int size = 2; size <= kp; size <<= 1) {
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      for (int i = tid; i < kp; i += 256) {
+        const int j = i ^ stride;
+        if (j > i) {
+          const bool desc = (i & size) == 0;
+          const unsigned long long x = win[i], y = win[j];
+          if ((x < y) == desc) { win[i] = y; win[j] = x; }
+        }
+      }
+      __syncthreads();
+    }
+  }
+  for (int i = tid; i < a.k; i += 256) {
+    const unsigned long long key = win[i];
+    const bool pad = key == 0ull;
+    a.out_scores[static_cast<size_t>(q) * a.k + i] =
+        pad ? -INFINITY : __uint_as_float(key_to_float_bits(static_cast<uint32_t>(key >> 32)));
+    a.out_idx[static_cast<size_t>(q) * a.k + i] =
+        pad ? -1 : static_cast<int64_t>(~static_cast<uint32_t>(key)) + a.row_offset;
+  }
+}
+
+// ============================================================================ cross-shard merge
 // One CTA per query: exact top-k of n = P*k candidates (P partial lists of k), sorted by
 // (score desc, index asc).  8-pass radix select on the 64-bit key (score key << 32 | ~idx),
 // then a bitonic sort of the k survivors in shared memory.
@@ -469,12 +597,13 @@ rescore_kernel(const __half* __restrict__ store, int64_t N, int D, const __half*
 // ============================================================================ host side
 struct ScanCore {  // one launch of topk_scan_kernel over N rows
   int epl, cap, num_qt, q_pad, num_slices, tiles_per_slice, grid;
-  size_t cand_bytes, part_score_bytes, part_idx_bytes;
 };
 struct ScanPlan {
   ScanCore main, pre;
-  int64_t n0;  // rows of the sample pre-pass (0: none)
-  size_t cand_bytes, part_score_bytes, part_idx_bytes, sample_score_bytes, sample_idx_bytes, total_bytes;
+  int64_t n0;   // rows of the sample pass (0: none)
+  int groups;   // n0 / 64
+  int select_cap;  // candidate keys the select kernel can hold in shared memory
+  size_t lists_bytes, counts_bytes, gmax_bytes, thresh_bytes, total_bytes;
 };
 
 static size_t up256(size_t x) { return (x + 255) & ~size_t(255); }
@@ -506,19 +635,19 @@ static void plan_core(int64_t N, int Q, int k, int sms, ScanCore* p) {
   p->num_slices = static_cast<int>((tiles + p->tiles_per_slice - 1) / p->tiles_per_slice);
   const long long items = static_cast<long long>(p->num_qt) * p->num_slices;
   p->grid = static_cast<int>(items < sms ? items : sms);
-  p->cand_bytes = up256(static_cast<size_t>(p->grid) * kScanQTile * p->cap * sizeof(int2));
-  p->part_score_bytes = up256(static_cast<size_t>(p->num_slices) * p->q_pad * k * sizeof(float));
-  p->part_idx_bytes = up256(static_cast<size_t>(p->num_slices) * p->q_pad * k * sizeof(int));
 }
 
-// Sample pre-pass: the exact top-k of the first n0 rows gives every query a lower bound on its global k-th best
-// score, so the main scan starts with a pass rate of ~k/n0 instead of admitting everything (and pruning) until its
-// own threshold settles.  n0 ~ the rows one SM sees at small query batch; < 1 % of the scan at any size.
-static int64_t sample_rows(int64_t N) {
+// Sample pass: the scan kernel runs over the first n0 rows recording only the maximum of every 64-row group; the
+// k-th largest group maximum of a query is a lower bound on its global k-th best score, so the full scan starts
+// with a pass rate of ~k/n0 instead of admitting (and pruning) everything until its own threshold settles.
+// n0 ~ the rows one SM sees at small query batch, <= 1/64 of larger stores: < 2 % of the scan.
+static int64_t sample_rows(int64_t N, int k) {
   if (N < 32768) return 0;
-  int64_t n0 = N / 8;
-  if (n0 > 65536) n0 = 65536;
-  return n0 & ~int64_t(kScanRowTile - 1);
+  int64_t n0 = N / 64 > 65536 ? N / 64 : 65536;
+  if (n0 > N / 4) n0 = N / 4;
+  n0 &= ~int64_t(kScanRowTile - 1);
+  if (n0 / 64 < 2 * static_cast<int64_t>(k)) return 0;
+  return n0;
 }
 
 static int plan_scan(int64_t N, int D, int Q, int k, ScanPlan* p) {
@@ -528,17 +657,18 @@ static int plan_scan(int64_t N, int D, int Q, int k, ScanPlan* p) {
   EVR_REQUIRE(k >= 1 && k <= kMaxFusedK, "top-k scan: k=%d must be in [1, %d]", k, kMaxFusedK);
   const int sms = sm_count();
   plan_core(N, Q, k, sms, &p->main);
-  p->n0 = sample_rows(N);
+  EVR_REQUIRE(p->main.num_slices <= 256, "top-k scan: %d slices exceed the select kernel's limit", p->main.num_slices);
+  p->n0 = sample_rows(N, k);
+  p->groups = static_cast<int>(p->n0 / 64);
   p->pre = ScanCore{};
   if (p->n0 > 0) plan_core(p->n0, Q, k, sms, &p->pre);
-  auto mx = [](size_t a, size_t b) { return a > b ? a : b; };
-  p->cand_bytes = mx(p->main.cand_bytes, p->pre.cand_bytes);
-  p->part_score_bytes = mx(p->main.part_score_bytes, p->pre.part_score_bytes);
-  p->part_idx_bytes = mx(p->main.part_idx_bytes, p->pre.part_idx_bytes);
-  p->sample_score_bytes = p->n0 > 0 ? up256(static_cast<size_t>(Q) * k * sizeof(float)) : 0;
-  p->sample_idx_bytes = p->n0 > 0 ? up256(static_cast<size_t>(Q) * k * sizeof(int64_t)) : 0;
-  p->total_bytes = p->cand_bytes + p->part_score_bytes + p->part_idx_bytes + p->sample_score_bytes +
-                   p->sample_idx_bytes + 256;
+  const long long worst = static_cast<long long>(p->main.num_slices) * p->main.cap;
+  p->select_cap = static_cast<int>(worst < 24576 ? worst : 24576);
+  p->lists_bytes = up256(static_cast<size_t>(p->main.num_slices) * p->main.q_pad * p->main.cap * sizeof(int2));
+  p->counts_bytes = up256(static_cast<size_t>(p->main.num_slices) * p->main.q_pad * sizeof(int));
+  p->gmax_bytes = p->n0 > 0 ? up256(static_cast<size_t>(p->main.q_pad) * p->groups * sizeof(float)) : 0;
+  p->thresh_bytes = up256(static_cast<size_t>(p->main.q_pad) * sizeof(float));
+  p->total_bytes = p->lists_bytes + p->counts_bytes + p->gmax_bytes + p->thresh_bytes + 256;
   return 0;
 }
 
@@ -596,14 +726,14 @@ extern "C" int evr_topk_workspace_bytes(int64_t N, int D, int Q, int k, size_t* 
 }
 
 static int run_scan(const ScanCore& c, const void* store, int64_t N, int D, const void* queries, int Q, int k,
-                    const float* init_thresh, int init_stride, int2* cand, float* part_score, int* part_idx,
+                    const float* init_thresh, int2* lists, int* counts, float* group_max, int groups,
                     cudaStream_t s) {
   ScanArgs a{};
   a.N = N; a.D = D; a.Q = Q; a.k = k;
   a.num_qt = c.num_qt; a.num_slices = c.num_slices; a.tiles_per_slice = c.tiles_per_slice; a.q_pad = c.q_pad;
   a.cap = c.cap;
-  a.init_thresh = init_thresh; a.init_stride = init_stride;
-  a.cand = cand; a.part_score = part_score; a.part_idx = part_idx;
+  a.init_thresh = init_thresh;
+  a.lists = lists; a.counts = counts; a.group_max = group_max; a.groups = groups;
   CUtensorMap tq, ts;
   if (int r = make_tmap_2d_16b(&tq, queries, Q, D, static_cast<uint64_t>(D) * 2, kScanQTile, false)) return r;
   if (int r = make_tmap_2d_16b(&ts, store, N, D, static_cast<uint64_t>(D) * 2, kScanRowTile, false)) return r;
@@ -630,23 +760,39 @@ extern "C" int evr_topk_search(const void* store, int64_t N, int D, int64_t row_
               p.total_bytes);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   uint8_t* ws = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~uintptr_t(255));
-  int2* cand = reinterpret_cast<int2*>(ws);
-  float* part_score = reinterpret_cast<float*>(ws + p.cand_bytes);
-  int* part_idx = reinterpret_cast<int*>(ws + p.cand_bytes + p.part_score_bytes);
-  float* sample_score = reinterpret_cast<float*>(ws + p.cand_bytes + p.part_score_bytes + p.part_idx_bytes);
-  int64_t* sample_idx = reinterpret_cast<int64_t*>(ws + p.cand_bytes + p.part_score_bytes + p.part_idx_bytes +
-                                                   p.sample_score_bytes);
+  int2* lists = reinterpret_cast<int2*>(ws);
+  int* counts = reinterpret_cast<int*>(ws + p.lists_bytes);
+  float* gmax = reinterpret_cast<float*>(ws + p.lists_bytes + p.counts_bytes);
+  float* thresh = reinterpret_cast<float*>(ws + p.lists_bytes + p.counts_bytes + p.gmax_bytes);
   const float* init = nullptr;
   if (p.n0 > 0) {
-    if (int r = run_scan(p.pre, store, p.n0, D, queries, Q, k, nullptr, 0, cand, part_score, part_idx, s)) return r;
-    if (int r = launch_final<int>(part_score, part_idx, p.pre.num_slices, p.pre.q_pad, Q, k, 0, sample_score,
-                                  sample_idx, s))
-      return r;
-    init = sample_score + (k - 1);  // k-th best of the sample
+    if (int r = run_scan(p.pre, store, p.n0, D, queries, Q, k, nullptr, nullptr, nullptr, gmax, p.groups, s)) return r;
+    {
+      ProfScope ps(PF_FINAL, s);
+      sample_kth_kernel<<<(Q + 7) / 8, 256, 0, s>>>(gmax, p.groups, Q, k, thresh);
+    }
+    EVR_CHECK_LAUNCH();
+    init = thresh;
   }
-  if (int r = run_scan(p.main, store, N, D, queries, Q, k, init, k, cand, part_score, part_idx, s)) return r;
-  return launch_final<int>(part_score, part_idx, p.main.num_slices, p.main.q_pad, Q, k, row_offset, out_scores,
-                           out_idx, s);
+  if (int r = run_scan(p.main, store, N, D, queries, Q, k, init, lists, counts, nullptr, 0, s)) return r;
+  SelectArgs sa{};
+  sa.lists = lists; sa.counts = counts;
+  sa.P = p.main.num_slices; sa.q_pad = p.main.q_pad; sa.cap = p.main.cap; sa.k = k; sa.smem_cap = p.select_cap;
+  sa.row_offset = row_offset; sa.out_scores = out_scores; sa.out_idx = out_idx;
+  int kp = 1;
+  while (kp < k) kp <<= 1;
+  const int sel_smem = (kp + p.select_cap) * 8;
+  static int sel_configured = 0;
+  if (sel_smem > 48 * 1024 && sel_smem > sel_configured) {
+    EVR_CHECK_CUDA(cudaFuncSetAttribute(topk_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sel_smem));
+    sel_configured = sel_smem;
+  }
+  {
+    ProfScope ps(PF_FINAL, s);
+    topk_select_kernel<<<Q, 256, sel_smem, s>>>(sa);
+  }
+  EVR_CHECK_LAUNCH();
+  return 0;
 }
 
 extern "C" int evr_topk_merge(const float* scores, const int64_t* idx, int P, int Q, int k, float* out_scores,
