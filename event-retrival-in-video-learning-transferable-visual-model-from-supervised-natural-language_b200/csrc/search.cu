@@ -383,7 +383,7 @@ topk_select_kernel(const SelectArgs a) {
   __shared__ unsigned hist[256];
   __shared__ int s_off[257];
   __shared__ unsigned long long s_prefix;
-  __shared__ int s_remaining, s_count;
+  __shared__ int s_remaining, s_count, s_done;
   const int q = blockIdx.x, tid = threadIdx.x;
   int kp = 1;
   while (kp < a.k) kp <<= 1;
@@ -397,7 +397,7 @@ topk_select_kernel(const SelectArgs a) {
   if (tid == 0) {
     int acc = 0;
     for (int i = 1; i <= a.P; ++i) { acc += s_off[i]; s_off[i] = acc; }
-    s_prefix = 0ull; s_remaining = a.k; s_count = 0;
+    s_prefix = 0ull; s_remaining = a.k; s_count = 0; s_done = 0;
   }
   __syncthreads();
   const int total = s_off[a.P];
@@ -439,19 +439,36 @@ topk_select_kernel(const SelectArgs a) {
         if ((key & himask) == prefix) atomicAdd(&hist[(key >> shift) & 255ull], 1u);
       });
       __syncthreads();
-      if (tid == 0) {
-        int rem = s_remaining, acc = 0, b = 255;
-        for (; b > 0; --b) {
-          if (acc + static_cast<int>(hist[b]) >= rem) break;
-          acc += hist[b];
+      if (warp == 0) {
+        // descending scan of the 256 bins: lane l owns bins 255-8l .. 248-8l
+        const int rem = s_remaining;
+        int loc[8], sum = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { loc[j] = static_cast<int>(hist[255 - 8 * lane - j]); sum += loc[j]; }
+        int incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const int t = __shfl_up_sync(0xffffffffu, incl, o);
+          if (lane >= o) incl += t;
         }
-        s_remaining = rem - acc;
-        s_prefix = prefix | (static_cast<unsigned long long>(b) << shift);
+        const int excl = incl - sum;
+        const bool mine = excl < rem && incl >= rem;  // the k-th key falls into one of this lane's bins
+        if (mine) {
+          int acc = excl, j = 0;
+          for (; j < 7; ++j) {
+            if (acc + loc[j] >= rem) break;
+            acc += loc[j];
+          }
+          s_remaining = rem - acc;
+          s_prefix = prefix | (static_cast<unsigned long long>(255 - 8 * lane - j) << shift);
+          s_done = (loc[j] == rem - acc);  // every key of that bin is a winner: lower digits need no pass
+        }
       }
       himask |= 255ull << shift;
       __syncthreads();
+      if (s_done) break;
     }
-    T = s_prefix;  // k-th largest key (keys are unique: the row id is part of the key)
+    T = s_prefix;  // winners are exactly the keys >= T (keys are unique: the row id is part of the key)
   }
   __syncthreads();
   for_each([&](unsigned long long key) {
@@ -629,6 +646,14 @@ static void plan_core(int64_t N, int Q, int k, int sms, ScanCore* p) {
       if (rounds < 2 && items < sms) eff *= 0.5;
       if (eff > best_eff + 1e-9) { best_eff = eff; best = s; }
     }
+    // the smallest slice count within 3 % of the best: fewer restarts of the per-item selection, fewer candidates
+    for (int s = 1; s <= best; ++s) {
+      const long long items = static_cast<long long>(p->num_qt) * s;
+      const long long rounds = (items + sms - 1) / sms;
+      double eff = static_cast<double>(items) / static_cast<double>(rounds * sms);
+      if (rounds < 2 && items < sms) eff *= 0.5;
+      if (eff >= 0.97 * best_eff) { best = s; break; }
+    }
     S = best;
   }
   p->tiles_per_slice = static_cast<int>((tiles + S - 1) / S);
@@ -663,7 +688,10 @@ static int plan_scan(int64_t N, int D, int Q, int k, ScanPlan* p) {
   p->pre = ScanCore{};
   if (p->n0 > 0) plan_core(p->n0, Q, k, sms, &p->pre);
   const long long worst = static_cast<long long>(p->main.num_slices) * p->main.cap;
-  p->select_cap = static_cast<int>(worst < 24576 ? worst : 24576);
+  // shared-memory budget of the select kernel: everything at small query batch (one CTA per query, ~15 k
+  // candidates), a few CTAs per SM at large batch; longer lists fall back to re-reading global memory
+  const long long budget = Q <= 256 ? 24576 : 6144;
+  p->select_cap = static_cast<int>(worst < budget ? worst : budget);
   p->lists_bytes = up256(static_cast<size_t>(p->main.num_slices) * p->main.q_pad * p->main.cap * sizeof(int2));
   p->counts_bytes = up256(static_cast<size_t>(p->main.num_slices) * p->main.q_pad * sizeof(int));
   p->gmax_bytes = p->n0 > 0 ? up256(static_cast<size_t>(p->main.q_pad) * p->groups * sizeof(float)) : 0;
