@@ -148,10 +148,16 @@ __device__ __forceinline__ uint32_t warp_prune(int2* buf, int cnt, int k, int la
   return T;
 }
 
-template <int EPL>
+// CG = 1: one CTA per SM, 128 queries x 128-row tiles.
+// CG = 2: CTA pairs (cta_group::2): 256 queries (128 per CTA) x 256-row tiles; each CTA streams only its 128 rows of
+//         every tile, so shared-memory and L2 traffic per FLOP are halved.  The leader (cluster rank 0) issues the
+//         MMAs and owns the TMA-arrival barriers; commits are multicast to both CTAs.
+template <int EPL, int CG>
 __global__ void __launch_bounds__(kScanThreads, 1)
 topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_s,
                  const ScanArgs args) {
+  constexpr int kRowTile = kScanRowTile * CG;    // store rows per tile (UMMA N)
+  constexpr int kAcc = kScanAccStages / CG;      // TMEM accumulator stages (512 columns in all)
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int num_kb = args.D / 64;
@@ -161,30 +167,40 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem_s + kScanStages * kScanStageBytes);
   uint64_t* full_bar = bars;                                         // [kScanStages]
   uint64_t* empty_bar = bars + kScanStages;                          // [kScanStages]
-  uint64_t* acc_full = bars + 2 * kScanStages;                       // [kScanAccStages]
-  uint64_t* acc_empty = bars + 2 * kScanStages + kScanAccStages;     // [kScanAccStages]
+  uint64_t* acc_full = bars + 2 * kScanStages;                       // [kAcc] (room for 4)
+  uint64_t* acc_empty = bars + 2 * kScanStages + kScanAccStages;     // [kAcc]
   uint64_t* q_full = bars + 2 * kScanStages + 2 * kScanAccStages;    // [1]
   uint64_t* q_empty = q_full + 1;                                    // [1]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(q_empty + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_items = args.num_qt * args.num_slices;
-  const int64_t total_tiles = (args.N + kScanRowTile - 1) / kScanRowTile;
+  const int64_t total_tiles = (args.N + kRowTile - 1) / kRowTile;
+  uint32_t rank = 0;
+  if constexpr (CG == 2) rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int unit = blockIdx.x / CG, num_units = gridDim.x / CG;  // a unit = one CTA or one CTA pair
+  if constexpr (CG == 2) cluster_sync_all();  // both CTAs resident before the pair-wide TMEM allocation
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_q);
     tma_prefetch_desc(&tmap_s);
   }
   if (warp == 1 && lane == 0) {
-    for (int i = 0; i < kScanStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
-    for (int i = 0; i < kScanAccStages; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4); }
-    mbar_init(q_full, 1);
+    // full / q_full / acc_empty collect one arrival per CTA of the unit (the peer arrives remotely on the leader's)
+    for (int i = 0; i < kScanStages; ++i) { mbar_init(&full_bar[i], CG); mbar_init(&empty_bar[i], 1); }
+    for (int i = 0; i < kAcc; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4 * CG); }
+    mbar_init(q_full, CG);
     mbar_init(q_empty, 1);
     fence_barrier_init();
   }
-  if (warp == 2) tmem_alloc<512>(tmem_slot);
+  if (warp == 2) {
+    if constexpr (CG == 2) tmem_alloc_pair<512>(tmem_slot);
+    else tmem_alloc<512>(tmem_slot);
+  }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (CG == 2) cluster_sync_all();
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -193,36 +209,50 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       // ===== TMA producer =====
       int stage = 0;
       uint32_t phase = 0, qphase = 0;
-      for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+      const uint64_t row_policy = args.num_qt > 1 ? kEvictNormal : kEvictFirst;
+      for (int item = unit; item < num_items; item += num_units) {
         const int qt = item % args.num_qt, slice = item / args.num_qt;
         mbar_wait(q_empty, qphase ^ 1);  // MMAs of the previous item no longer read the query tile
-        mbar_expect_tx(q_full, q_bytes);
-        for (int kb = 0; kb < num_kb; ++kb)
-          tma_load_2d(smem_q + kb * kScanStageBytes, &tmap_q, q_full, kb * 64, qt * kScanQTile, kEvictLast);
+        const int q_row = (qt * CG + static_cast<int>(rank)) * kScanQTile;
+        if constexpr (CG == 2) {
+          for (int kb = 0; kb < num_kb; ++kb)
+            tma_load_2d_pair(smem_q + kb * kScanStageBytes, &tmap_q, q_full, kb * 64, q_row, kEvictLast);
+          if (leader) mbar_expect_tx(q_full, q_bytes * 2);
+          else mbar_arrive_cluster(q_full, 0);
+        } else {
+          mbar_expect_tx(q_full, q_bytes);
+          for (int kb = 0; kb < num_kb; ++kb)
+            tma_load_2d(smem_q + kb * kScanStageBytes, &tmap_q, q_full, kb * 64, q_row, kEvictLast);
+        }
         qphase ^= 1;
         const int64_t t0 = static_cast<int64_t>(slice) * args.tiles_per_slice;
         int64_t t1 = t0 + args.tiles_per_slice;
         if (t1 > total_tiles) t1 = total_tiles;
         for (int64_t t = t0; t < t1; ++t) {
-          const int row = static_cast<int>(t * kScanRowTile);
+          const int row = static_cast<int>(t * kRowTile) + static_cast<int>(rank) * kScanRowTile;  // this CTA's half
           for (int kb = 0; kb < num_kb; ++kb) {
             mbar_wait(&empty_bar[stage], phase ^ 1);
-            mbar_expect_tx(&full_bar[stage], kScanStageBytes);
-            tma_load_2d(smem_s + stage * kScanStageBytes, &tmap_s, &full_bar[stage], kb * 64, row,
-                        args.num_qt > 1 ? kEvictNormal : kEvictFirst);
+            if constexpr (CG == 2) {
+              tma_load_2d_pair(smem_s + stage * kScanStageBytes, &tmap_s, &full_bar[stage], kb * 64, row, row_policy);
+              if (leader) mbar_expect_tx(&full_bar[stage], kScanStageBytes * 2);
+              else mbar_arrive_cluster(&full_bar[stage], 0);
+            } else {
+              mbar_expect_tx(&full_bar[stage], kScanStageBytes);
+              tma_load_2d(smem_s + stage * kScanStageBytes, &tmap_s, &full_bar[stage], kb * 64, row, row_policy);
+            }
             if (++stage == kScanStages) { stage = 0; phase ^= 1; }
           }
         }
       }
     }
   } else if (warp == 1) {
-    if (elect_one()) {
-      // ===== MMA issuer =====
-      constexpr uint32_t idesc = umma_idesc_f16(/*fp16*/ 0, kScanQTile, kScanRowTile);
+    if (leader && elect_one()) {
+      // ===== MMA issuer (leader CTA only) =====
+      constexpr uint32_t idesc = umma_idesc_f16(/*fp16*/ 0, kScanQTile * CG, kRowTile);
       int stage = 0, as = 0;
       uint32_t phase = 0, aphase = 0, qphase = 0;
       const uint32_t q_addr = smem_u32(smem_q);
-      for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+      for (int item = unit; item < num_items; item += num_units) {
         const int slice = item / args.num_qt;
         mbar_wait(q_full, qphase);
         qphase ^= 1;
@@ -233,33 +263,39 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         for (int64_t t = t0; t < t1; ++t) {
           mbar_wait(&acc_empty[as], aphase ^ 1);
           tc_fence_after();
-          const uint32_t d_tmem = tmem_base + as * kScanRowTile;
+          const uint32_t d_tmem = tmem_base + as * kRowTile;
           for (int kb = 0; kb < num_kb; ++kb) {
             mbar_wait(&full_bar[stage], phase);
             tc_fence_after();
             const uint64_t a_desc = umma_smem_desc_sw128(q_addr + kb * kScanStageBytes);
             const uint64_t b_desc = umma_smem_desc_sw128(smem_u32(smem_s + stage * kScanStageBytes));
 #pragma unroll
-            for (int k = 0; k < 4; ++k) umma_f16(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
-            umma_commit(&empty_bar[stage]);
+            for (int k = 0; k < 4; ++k) {
+              if constexpr (CG == 2) umma_f16_pair(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
+              else umma_f16(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
+            }
+            if constexpr (CG == 2) umma_commit_pair(&empty_bar[stage]);
+            else umma_commit(&empty_bar[stage]);
             if (++stage == kScanStages) { stage = 0; phase ^= 1; }
           }
-          umma_commit(&acc_full[as]);
-          if (++as == kScanAccStages) { as = 0; aphase ^= 1; }
+          if constexpr (CG == 2) umma_commit_pair(&acc_full[as]);
+          else umma_commit(&acc_full[as]);
+          if (++as == kAcc) { as = 0; aphase ^= 1; }
         }
-        umma_commit(q_empty);
+        if constexpr (CG == 2) umma_commit_pair(q_empty);
+        else umma_commit(q_empty);
       }
     }
   } else {
     // ===== epilogue / selection: warps 2..5, TMEM lane quadrant = warp % 4 =====
     const int quad = warp & 3;
     const int k = args.k, cap = args.cap;
-    const int trigger = cap - kScanRowTile;
+    const int trigger = cap - kRowTile;
     int as = 0;
     uint32_t aphase = 0;
-    for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+    for (int item = unit; item < num_items; item += num_units) {
       const int qt = item % args.num_qt, slice = item / args.num_qt;
-      const int q0 = qt * kScanQTile + quad * 32;  // first query of this warp
+      const int q0 = (qt * CG + static_cast<int>(rank)) * kScanQTile + quad * 32;  // first query of this warp
       const bool q_valid = q0 + lane < args.Q;
       // the candidate list of (slice, query) is filled in place; the final select kernel reads it with its count
       int2* const cand_warp = args.lists + (static_cast<size_t>(slice) * args.q_pad + q0) * cap;
@@ -276,12 +312,12 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       for (int64_t t = t0; t < t1; ++t) {
         mbar_wait(&acc_full[as], aphase);
         tc_fence_after();
-        const int row_base = static_cast<int>(t * kScanRowTile);
+        const int row_base = static_cast<int>(t * kRowTile);
         const int rows_left = static_cast<int>(args.N - row_base);  // > 0
 #pragma unroll 1
-        for (int c = 0; c < kScanRowTile / 64; ++c) {
+        for (int c = 0; c < kRowTile / 64; ++c) {
           uint32_t v[2][32];
-          const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + as * kScanRowTile + c * 64;
+          const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + as * kRowTile + c * 64;
           tmem_ld_32x32(taddr, v[0]);
           tmem_ld_32x32(taddr + 32, v[1]);
           tmem_ld_wait();
@@ -310,12 +346,15 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             }
           }
           if (args.group_max != nullptr && q_valid)  // sample pass: N is a multiple of the tile, no padding rows
-            args.group_max[static_cast<size_t>(q0 + lane) * args.groups + (t * (kScanRowTile / 64) + c)] = gmx;
+            args.group_max[static_cast<size_t>(q0 + lane) * args.groups + (t * (kRowTile / 64) + c)] = gmx;
         }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&acc_empty[as]);  // release TMEM before any pruning
-        if (++as == kScanAccStages) { as = 0; aphase ^= 1; }
+        if (lane == 0) {  // release TMEM before any pruning (the leader's barrier gates the MMA issuer)
+          if (leader) mbar_arrive(&acc_empty[as]);
+          else mbar_arrive_cluster(&acc_empty[as], 0);
+        }
+        if (++as == kAcc) { as = 0; aphase ^= 1; }
 
         uint32_t need = __ballot_sync(0xffffffffu, cnt > trigger);
         while (need) {
@@ -335,10 +374,12 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   }
 
   tc_fence_before();
-  __syncthreads();
+  if constexpr (CG == 2) cluster_sync_all();  // the peer's remote arrivals and MMA reads of our smem are done
+  else __syncthreads();
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc<512>(tmem_base);
+    if constexpr (CG == 2) tmem_dealloc_pair<512>(tmem_base);
+    else tmem_dealloc<512>(tmem_base);
   }
 }
 
@@ -613,6 +654,7 @@ rescore_kernel(const __half* __restrict__ store, int64_t N, int D, const __half*
 
 // ============================================================================ host side
 struct ScanCore {  // one launch of topk_scan_kernel over N rows
+  int cg;  // 1: one CTA per unit, 2: CTA pairs (cta_group::2)
   int epl, cap, num_qt, q_pad, num_slices, tiles_per_slice, grid;
 };
 struct ScanPlan {
@@ -625,12 +667,17 @@ struct ScanPlan {
 
 static size_t up256(size_t x) { return (x + 255) & ~size_t(255); }
 
-static void plan_core(int64_t N, int Q, int k, int sms, ScanCore* p) {
+static void plan_core(int64_t N, int Q, int k, int sm_total, ScanCore* p) {
+  // more than one 128-query tile: CTA pairs (256 queries x 256-row tiles) halve the operand traffic per FLOP;
+  // a single tile is HBM-bound and keeps one CTA per SM so every SM streams its own slice
+  p->cg = (Q > kScanQTile && sm_total % 2 == 0) ? 2 : 1;
+  const int sms = sm_total / p->cg;  // units
+  const int qtile = kScanQTile * p->cg, rowtile = kScanRowTile * p->cg;
   p->epl = k <= 128 ? 16 : 64;
   p->cap = 32 * p->epl;
-  p->num_qt = (Q + kScanQTile - 1) / kScanQTile;
-  p->q_pad = p->num_qt * kScanQTile;
-  const int64_t tiles = (N + kScanRowTile - 1) / kScanRowTile;
+  p->num_qt = (Q + qtile - 1) / qtile;
+  p->q_pad = p->num_qt * qtile;
+  const int64_t tiles = (N + rowtile - 1) / rowtile;
   int S;
   if (p->num_qt == 1) {
     S = static_cast<int>(tiles < sms ? tiles : sms);
@@ -659,7 +706,7 @@ static void plan_core(int64_t N, int Q, int k, int sms, ScanCore* p) {
   p->tiles_per_slice = static_cast<int>((tiles + S - 1) / S);
   p->num_slices = static_cast<int>((tiles + p->tiles_per_slice - 1) / p->tiles_per_slice);
   const long long items = static_cast<long long>(p->num_qt) * p->num_slices;
-  p->grid = static_cast<int>(items < sms ? items : sms);
+  p->grid = static_cast<int>(items < sms ? items : sms) * p->cg;
 }
 
 // Sample pass: the scan kernel runs over the first n0 rows recording only the maximum of every 64-row group; the
@@ -670,7 +717,7 @@ static int64_t sample_rows(int64_t N, int k) {
   if (N < 32768) return 0;
   int64_t n0 = N / 64 > 65536 ? N / 64 : 65536;
   if (n0 > N / 4) n0 = N / 4;
-  n0 &= ~int64_t(kScanRowTile - 1);
+  n0 &= ~int64_t(2 * kScanRowTile - 1);  // whole tiles for CTA pairs too: the sample pass sees no padding rows
   if (n0 / 64 < 2 * static_cast<int64_t>(k)) return 0;
   return n0;
 }
@@ -712,16 +759,28 @@ static int launch_final(const float* scores, const IdxT* idx, int P, int q_strid
   return 0;
 }
 
-template <int EPL>
+template <int EPL, int CG>
 static int launch_scan(int grid, int smem, cudaStream_t s, const CUtensorMap& tq, const CUtensorMap& ts,
                        const ScanArgs& a) {
-  auto kern = topk_scan_kernel<EPL>;
+  auto kern = topk_scan_kernel<EPL, CG>;
   static int configured = 0;  // per instantiation
   if (smem > configured) {
     EVR_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = smem;
   }
-  kern<<<grid, kScanThreads, smem, s>>>(tq, ts, a);
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kScanThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CG;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  EVR_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, tq, ts, a));
   return 0;
 }
 
@@ -768,11 +827,10 @@ static int run_scan(const ScanCore& c, const void* store, int64_t N, int D, cons
   const int smem = kScanQTile * D * 2 + kScanStages * kScanStageBytes + 1024 + 256;
   {
     ProfScope ps(PF_SCAN, s);
-    if (c.epl == 16) {
-      if (int r = launch_scan<16>(c.grid, smem, s, tq, ts, a)) return r;
-    } else {
-      if (int r = launch_scan<64>(c.grid, smem, s, tq, ts, a)) return r;
-    }
+    int r;
+    if (c.cg == 2) r = c.epl == 16 ? launch_scan<16, 2>(c.grid, smem, s, tq, ts, a) : launch_scan<64, 2>(c.grid, smem, s, tq, ts, a);
+    else r = c.epl == 16 ? launch_scan<16, 1>(c.grid, smem, s, tq, ts, a) : launch_scan<64, 1>(c.grid, smem, s, tq, ts, a);
+    if (r) return r;
   }
   EVR_CHECK_LAUNCH();
   return 0;
