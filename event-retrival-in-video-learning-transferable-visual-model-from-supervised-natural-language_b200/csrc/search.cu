@@ -335,12 +335,19 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             const float mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
             gmx = fmaxf(gmx, mx);
             if (args.group_max == nullptr && mx >= thresh) {  // rare once the threshold has settled
+              // only the 8-column groups whose own maximum passes are walked (the warp pays for a group when any
+              // of its 32 queries admits from it: ~4x fewer predicated stores than walking all 32 columns)
 #pragma unroll
-              for (int j = 0; j < 32; ++j) {
-                const int r = c * 64 + h * 32 + j;
-                if (__uint_as_float(v[h][j]) >= thresh && r < rows_left) {
-                  __stcg(buf + cnt, make_int2(static_cast<int>(v[h][j]), row_base + r));
-                  ++cnt;
+              for (int u = 0; u < 4; ++u) {
+                if (m4[u] >= thresh) {
+#pragma unroll
+                  for (int j = 8 * u; j < 8 * u + 8; ++j) {
+                    const int r = c * 64 + h * 32 + j;
+                    if (__uint_as_float(v[h][j]) >= thresh && r < rows_left) {
+                      __stcg(buf + cnt, make_int2(static_cast<int>(v[h][j]), row_base + r));
+                      ++cnt;
+                    }
+                  }
                 }
               }
             }
@@ -713,9 +720,16 @@ static void plan_core(int64_t N, int Q, int k, int sm_total, ScanCore* p) {
 // k-th largest group maximum of a query is a lower bound on its global k-th best score, so the full scan starts
 // with a pass rate of ~k/n0 instead of admitting (and pruning) everything until its own threshold settles.
 // n0 ~ the rows one SM sees at small query batch, <= 1/64 of larger stores: < 2 % of the scan.
-static int64_t sample_rows(int64_t N, int k) {
+static int64_t sample_rows(int64_t N, int k, int Q) {
   if (N < 32768) return 0;
-  int64_t n0 = N / 64 > 65536 ? N / 64 : 65536;
+  int64_t n0 = 65536;
+  if (Q > kScanQTile) {
+    // tensor-bound regime: the epilogue's cost is the admissions, so buy a tighter threshold with a larger sample
+    // (pass rate k/n0 ~ 3e-4; the sample pass itself admits nothing and runs at full MMA rate)
+    n0 = 3072ll * k;
+    if (n0 > N / 16) n0 = N / 16;
+    if (n0 < 65536) n0 = 65536;
+  }
   if (n0 > N / 4) n0 = N / 4;
   n0 &= ~int64_t(2 * kScanRowTile - 1);  // whole tiles for CTA pairs too: the sample pass sees no padding rows
   if (n0 / 64 < 2 * static_cast<int64_t>(k)) return 0;
@@ -730,7 +744,7 @@ static int plan_scan(int64_t N, int D, int Q, int k, ScanPlan* p) {
   const int sms = sm_count();
   plan_core(N, Q, k, sms, &p->main);
   EVR_REQUIRE(p->main.num_slices <= 256, "top-k scan: %d slices exceed the select kernel's limit", p->main.num_slices);
-  p->n0 = sample_rows(N, k);
+  p->n0 = sample_rows(N, k, Q);
   p->groups = static_cast<int>(p->n0 / 64);
   p->pre = ScanCore{};
   if (p->n0 > 0) plan_core(p->n0, Q, k, sms, &p->pre);
