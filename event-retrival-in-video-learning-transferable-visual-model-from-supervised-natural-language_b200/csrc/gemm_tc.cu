@@ -6,46 +6,58 @@
 
 namespace evr {
 
-template <int BLOCK_N, int EPI>
+template <int BLOCK_N, int EPI, int CG>
 static int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const GemmArgs& args, int grid,
                       cudaStream_t stream) {
-  using Cfg = GemmCfg<BLOCK_N, EPI>;
-  auto kern = gemm_tc_kernel<BLOCK_N, EPI>;
+  using Cfg = GemmCfg<BLOCK_N, EPI, CG>;
+  auto kern = gemm_tc_kernel<BLOCK_N, EPI, CG>;
   static bool attr_set = false;  // per instantiation
   if (!attr_set) {
     EVR_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
     attr_set = true;
   }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CG;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
   ProfScope ps(PF_GEMM, stream);
-  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(ta, tb, args);
+  EVR_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, args));
   EVR_CHECK_LAUNCH();
   return 0;
 }
 
-template <int BLOCK_N>
+template <int BLOCK_N, int CG>
 static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const GemmArgs& args, int epilogue, int grid,
                       cudaStream_t stream) {
   switch (epilogue) {
-    case EPI_BF16: return launch_one<BLOCK_N, EPI_BF16>(ta, tb, args, grid, stream);
-    case EPI_BF16_GELU: return launch_one<BLOCK_N, EPI_BF16_GELU>(ta, tb, args, grid, stream);
-    case EPI_F32_RESID: return launch_one<BLOCK_N, EPI_F32_RESID>(ta, tb, args, grid, stream);
-    case EPI_F32: return launch_one<BLOCK_N, EPI_F32>(ta, tb, args, grid, stream);
-    case EPI_PATCH: return launch_one<BLOCK_N, EPI_PATCH>(ta, tb, args, grid, stream);
+    case EPI_BF16: return launch_one<BLOCK_N, EPI_BF16, CG>(ta, tb, args, grid, stream);
+    case EPI_BF16_GELU: return launch_one<BLOCK_N, EPI_BF16_GELU, CG>(ta, tb, args, grid, stream);
+    case EPI_F32_RESID: return launch_one<BLOCK_N, EPI_F32_RESID, CG>(ta, tb, args, grid, stream);
+    case EPI_F32: return launch_one<BLOCK_N, EPI_F32, CG>(ta, tb, args, grid, stream);
+    case EPI_PATCH: return launch_one<BLOCK_N, EPI_PATCH, CG>(ta, tb, args, grid, stream);
   }
   set_error("unknown GEMM epilogue %d", epilogue);
   return 2;
 }
 
-// Pick the N tile that wastes the fewest SM-rounds (wave quantisation over the persistent grid).
-static int choose_block_n(int M, int N, int sms) {
-  const int num_m = (M + kGemmBlockM - 1) / kGemmBlockM;
+// Pick the N tile that wastes the fewest rounds (wave quantisation over the persistent grid of `units`).
+static int choose_block_n(int M, int N, int units, int tile_m) {
+  const int num_m = (M + tile_m - 1) / tile_m;
   const int cands[3] = {256, 192, 128};
   int best = 128;
   double best_cost = 1e30;
   for (int bn : cands) {
     const int tiles = num_m * ((N + bn - 1) / bn);
-    const int rounds = (tiles + sms - 1) / sms;
-    // time per tile ~ BLOCK_N; narrow tiles pay more smem bandwidth per MMA
+    const int rounds = (tiles + units - 1) / units;
+    // time per tile ~ BLOCK_N; narrow tiles move more operand bytes per FLOP
     double cost = static_cast<double>(rounds) * bn * (bn == 128 ? 1.06 : 1.0);
     if (cost < best_cost) { best_cost = cost; best = bn; }
   }
@@ -59,17 +71,27 @@ int launch_gemm_bf16(const void* A, int lda, const void* W, int ldw, const GemmA
   EVR_REQUIRE(args.N % 32 == 0, "GEMM: N=%d must be a multiple of 32", args.N);
   EVR_REQUIRE(args.ldo % 8 == 0, "GEMM: ldo=%d must be a multiple of 8", args.ldo);
   const int sms = sm_count();
-  const int bn = choose_block_n(args.M, args.N, sms);
+  // CTA pairs (256-row tiles) whenever there is more than one 128-row tile of work
+  const int cg = (args.M > kGemmBlockM && sms % 2 == 0) ? 2 : 1;
+  const int units = sms / cg, tile_m = kGemmBlockM * cg;
+  const int bn = choose_block_n(args.M, args.N, units, tile_m);
   CUtensorMap ta, tb;
   if (int r = make_tmap_2d_16b(&ta, A, args.M, args.K, static_cast<uint64_t>(lda) * 2, kGemmBlockM, true)) return r;
-  if (int r = make_tmap_2d_16b(&tb, W, args.N, args.K, static_cast<uint64_t>(ldw) * 2, bn, true)) return r;
-  const int num_m = (args.M + kGemmBlockM - 1) / kGemmBlockM;
+  if (int r = make_tmap_2d_16b(&tb, W, args.N, args.K, static_cast<uint64_t>(ldw) * 2, bn / cg, true)) return r;
+  const int num_m = (args.M + tile_m - 1) / tile_m;
   const int tiles = num_m * ((args.N + bn - 1) / bn);
-  const int grid = tiles < sms ? tiles : sms;
+  const int grid = (tiles < units ? tiles : units) * cg;
+  if (cg == 2) {
+    switch (bn) {
+      case 256: return launch_epi<256, 2>(ta, tb, args, epilogue, grid, stream);
+      case 192: return launch_epi<192, 2>(ta, tb, args, epilogue, grid, stream);
+      default: return launch_epi<128, 2>(ta, tb, args, epilogue, grid, stream);
+    }
+  }
   switch (bn) {
-    case 256: return launch_epi<256>(ta, tb, args, epilogue, grid, stream);
-    case 192: return launch_epi<192>(ta, tb, args, epilogue, grid, stream);
-    default: return launch_epi<128>(ta, tb, args, epilogue, grid, stream);
+    case 256: return launch_epi<256, 1>(ta, tb, args, epilogue, grid, stream);
+    case 192: return launch_epi<192, 1>(ta, tb, args, epilogue, grid, stream);
+    default: return launch_epi<128, 1>(ta, tb, args, epilogue, grid, stream);
   }
 }
 

@@ -53,10 +53,13 @@ struct EpiCfg {
   static constexpr int kUnitsPerRow = kRowBytes / 16;     // 8 | 16
 };
 
-template <int BLOCK_N, int EPI>
+// CG = 1: one CTA per 128 x BLOCK_N tile.  CG = 2: a CTA pair (cta_group::2) per 256 x BLOCK_N tile; each CTA stages its
+// 128 rows of A and its half of the BLOCK_N weight rows, halving shared-memory and L2 operand traffic per FLOP.
+template <int BLOCK_N, int EPI, int CG>
 struct GemmCfg {
   static constexpr int kABytes = kGemmBlockM * kGemmBlockK * 2;
-  static constexpr int kBBytes = BLOCK_N * kGemmBlockK * 2;
+  static constexpr int kBRows = BLOCK_N / CG;  // weight rows staged by one CTA
+  static constexpr int kBBytes = kBRows * kGemmBlockK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kEpiBytes = EpiCfg<EPI>::kBytes;
   static constexpr int kStages = (227 * 1024 - 1024 - 256 - kEpiBytes) / kStageBytes;
@@ -72,8 +75,12 @@ struct GemmCfg {
 };
 
 __device__ __forceinline__ float quick_gelu(float x) {
-  // clip/model.py QuickGELU: x * sigmoid(1.702 x)   (MUFU.EX2 + MUFU.RCP; the IEEE reciprocal costs 3x the epilogue)
-  return __fdividef(x, 1.0f + __expf(-1.702f * x));
+  // clip/model.py QuickGELU: x * sigmoid(1.702 x) = 0.5 x (1 + tanh(0.851 x)): one MUFU.TANH (rel. error 2^-11,
+  // below the bf16 output's 2^-9) instead of EX2 + RCP
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(0.851f * x));
+  const float h = 0.5f * x;
+  return fmaf(h, t, h);
 }
 
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
@@ -81,11 +88,11 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&t);
 }
 
-template <int BLOCK_N, int EPI>
+template <int BLOCK_N, int EPI, int CG>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const GemmArgs args) {
-  using Cfg = GemmCfg<BLOCK_N, EPI>;
+  using Cfg = GemmCfg<BLOCK_N, EPI, CG>;
   using Epi = EpiCfg<EPI>;
   constexpr int kStages = Cfg::kStages;
   extern __shared__ uint8_t smem_raw[];
@@ -100,7 +107,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int num_m = (args.M + kGemmBlockM - 1) / kGemmBlockM;
+  constexpr int kTileM = kGemmBlockM * CG;
+  const int num_m = (args.M + kTileM - 1) / kTileM;
+  uint32_t rank = 0;
+  if constexpr (CG == 2) rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int unit = blockIdx.x / CG, num_units = gridDim.x / CG;
+  if constexpr (CG == 2) cluster_sync_all();  // both CTAs resident before the pair-wide TMEM allocation
   const int num_n = (args.N + BLOCK_N - 1) / BLOCK_N;
   const int num_tiles = num_m * num_n;
   const int num_kb = args.K / kGemmBlockK;
@@ -111,18 +124,22 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < kStages; ++i) {
-      mbar_init(&full_bar[i], 1);
+      mbar_init(&full_bar[i], CG);  // one arrival per CTA of the unit, on the leader's barrier
       mbar_init(&empty_bar[i], 1);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tmem_full[i], 1);
-      mbar_init(&tmem_empty[i], 4);  // one arrive per epilogue warp
+      mbar_init(&tmem_empty[i], 4 * CG);  // one arrive per epilogue warp of the unit
     }
     fence_barrier_init();
   }
-  if (warp == 2) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+  if (warp == 2) {
+    if constexpr (CG == 2) tmem_alloc_pair<Cfg::kTmemCols>(tmem_slot);
+    else tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+  }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (CG == 2) cluster_sync_all();
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -131,28 +148,37 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       // ===== TMA producer =====
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int tile = unit; tile < num_tiles; tile += num_units) {
         const int m_idx = tile % num_m, n_idx = tile / num_m;
+        const int a_row = m_idx * kTileM + static_cast<int>(rank) * kGemmBlockM;
+        const int b_row = n_idx * BLOCK_N + static_cast<int>(rank) * Cfg::kBRows;
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * Cfg::kStageBytes;
           uint8_t* sb = sa + Cfg::kABytes;
-          mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
-          tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kGemmBlockK, m_idx * kGemmBlockM, kEvictNormal);
-          tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * kGemmBlockK, n_idx * BLOCK_N, kEvictLast);
+          if constexpr (CG == 2) {
+            tma_load_2d_pair(sa, &tmap_a, &full_bar[stage], kb * kGemmBlockK, a_row, kEvictNormal);
+            tma_load_2d_pair(sb, &tmap_b, &full_bar[stage], kb * kGemmBlockK, b_row, kEvictLast);
+            if (leader) mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes * 2);
+            else mbar_arrive_cluster(&full_bar[stage], 0);
+          } else {
+            mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+            tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kGemmBlockK, a_row, kEvictNormal);
+            tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * kGemmBlockK, b_row, kEvictLast);
+          }
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    if (elect_one()) {
-      // ===== MMA issuer =====
-      constexpr uint32_t idesc = umma_idesc_f16(/*bf16*/ 1, kGemmBlockM, BLOCK_N);
+    if (leader && elect_one()) {
+      // ===== MMA issuer (leader CTA only) =====
+      constexpr uint32_t idesc = umma_idesc_f16(/*bf16*/ 1, kTileM, BLOCK_N);
       int stage = 0;
       uint32_t phase = 0;
       int as = 0;
       uint32_t aphase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int tile = unit; tile < num_tiles; tile += num_units) {
         mbar_wait(&tmem_empty[as], aphase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * BLOCK_N;
@@ -165,12 +191,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 #pragma unroll
           for (int k = 0; k < kGemmBlockK / 16; ++k) {
             // 16 bf16 = 32 B along K inside the swizzle atom -> +2 in the (addr >> 4) field
-            umma_f16(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
+            if constexpr (CG == 2) umma_f16_pair(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
+            else umma_f16(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
           }
-          umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs retire
+          // frees the smem slot (in both CTAs) once these MMAs retire
+          if constexpr (CG == 2) umma_commit_pair(&empty_bar[stage]);
+          else umma_commit(&empty_bar[stage]);
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&tmem_full[as]);  // accumulator complete
+        if constexpr (CG == 2) umma_commit_pair(&tmem_full[as]);  // accumulator complete
+        else umma_commit(&tmem_full[as]);
         as ^= 1;
         if (as == 0) aphase ^= 1;
       }
@@ -182,11 +212,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     uint8_t* my_row = stage + lane * Epi::kPitch;
     int as = 0;
     uint32_t aphase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int tile = unit; tile < num_tiles; tile += num_units) {
       const int m_idx = tile % num_m, n_idx = tile / num_m;
       mbar_wait(&tmem_full[as], aphase);
       tc_fence_after();
-      const int row0 = m_idx * kGemmBlockM + q * 32;  // first row of this warp
+      const int row0 = m_idx * kTileM + static_cast<int>(rank) * kGemmBlockM + q * 32;  // first row of this warp
 #pragma unroll 1
       for (int c = 0; c < BLOCK_N / kEpiCols; ++c) {
         const int col0 = n_idx * BLOCK_N + c * kEpiCols;
@@ -235,30 +265,56 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         // ---- coalesced copy-out: 16-B units, consecutive lanes walk along a row
         constexpr int kUnits = 32 * Epi::kUnitsPerRow;
         constexpr int kColsPerUnit = 16 / Epi::kElt;
+        constexpr int kIters = kUnits / 32;  // 8 (bf16) | 16 (fp32)
+        if constexpr (EPI == EPI_F32_RESID) {
+          // read-modify-write of the fp32 residual stream: all loads of a batch are issued before the first store
+          // (the compiler cannot reorder them itself: the accesses are in place)
 #pragma unroll
-        for (int it = 0; it < kUnits / 32; ++it) {
-          const int u = it * 32 + lane;
-          const int r = u / Epi::kUnitsPerRow, cu = u % Epi::kUnitsPerRow;
-          const int row = row0 + r, col = col0 + cu * kColsPerUnit;
-          if (row < args.M && col < args.N) {
-            const uint4 sv = *reinterpret_cast<const uint4*>(stage + r * Epi::kPitch + cu * 16);
-            if constexpr (Epi::kOutBf16) {
-              *reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(args.out) + static_cast<size_t>(row) * args.ldo + col) = sv;
-            } else {
-              float4 x = *reinterpret_cast<const float4*>(&sv);
-              size_t out_row = row;
-              if constexpr (EPI == EPI_PATCH) {
-                const int bimg = row / args.patches, pp = row - bimg * args.patches;
-                out_row = static_cast<size_t>(bimg) * (args.patches + 1) + 1 + pp;
-                const float4 pe = __ldg(reinterpret_cast<const float4*>(args.pos + static_cast<size_t>(1 + pp) * args.N + col));
-                x.x += pe.x; x.y += pe.y; x.z += pe.z; x.w += pe.w;
+          for (int half = 0; half < 2; ++half) {
+            float4 old[kIters / 2];
+#pragma unroll
+            for (int i = 0; i < kIters / 2; ++i) {
+              const int u = (half * (kIters / 2) + i) * 32 + lane;
+              const int r = u / Epi::kUnitsPerRow, cu = u % Epi::kUnitsPerRow;
+              const int row = row0 + r, col = col0 + cu * kColsPerUnit;
+              old[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (row < args.M && col < args.N)
+                old[i] = __ldcg(reinterpret_cast<const float4*>(static_cast<const float*>(args.out) +
+                                                                static_cast<size_t>(row) * args.ldo + col));
+            }
+#pragma unroll
+            for (int i = 0; i < kIters / 2; ++i) {
+              const int u = (half * (kIters / 2) + i) * 32 + lane;
+              const int r = u / Epi::kUnitsPerRow, cu = u % Epi::kUnitsPerRow;
+              const int row = row0 + r, col = col0 + cu * kColsPerUnit;
+              if (row < args.M && col < args.N) {
+                float4 x = *reinterpret_cast<const float4*>(stage + r * Epi::kPitch + cu * 16);
+                x.x += old[i].x; x.y += old[i].y; x.z += old[i].z; x.w += old[i].w;
+                *reinterpret_cast<float4*>(static_cast<float*>(args.out) + static_cast<size_t>(row) * args.ldo + col) = x;
               }
-              float4* o = reinterpret_cast<float4*>(static_cast<float*>(args.out) + out_row * args.ldo + col);
-              if constexpr (EPI == EPI_F32_RESID) {
-                const float4 old = *o;
-                x.x += old.x; x.y += old.y; x.z += old.z; x.w += old.w;
+            }
+          }
+        } else {
+#pragma unroll
+          for (int it = 0; it < kIters; ++it) {
+            const int u = it * 32 + lane;
+            const int r = u / Epi::kUnitsPerRow, cu = u % Epi::kUnitsPerRow;
+            const int row = row0 + r, col = col0 + cu * kColsPerUnit;
+            if (row < args.M && col < args.N) {
+              const uint4 sv = *reinterpret_cast<const uint4*>(stage + r * Epi::kPitch + cu * 16);
+              if constexpr (Epi::kOutBf16) {
+                *reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(args.out) + static_cast<size_t>(row) * args.ldo + col) = sv;
+              } else {
+                float4 x = *reinterpret_cast<const float4*>(&sv);
+                size_t out_row = row;
+                if constexpr (EPI == EPI_PATCH) {
+                  const int bimg = row / args.patches, pp = row - bimg * args.patches;
+                  out_row = static_cast<size_t>(bimg) * (args.patches + 1) + 1 + pp;
+                  const float4 pe = __ldg(reinterpret_cast<const float4*>(args.pos + static_cast<size_t>(1 + pp) * args.N + col));
+                  x.x += pe.x; x.y += pe.y; x.z += pe.z; x.w += pe.w;
+                }
+                *reinterpret_cast<float4*>(static_cast<float*>(args.out) + out_row * args.ldo + col) = x;
               }
-              *o = x;
             }
           }
         }
@@ -266,17 +322,22 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tmem_empty[as]);
+      if (lane == 0) {
+        if (leader) mbar_arrive(&tmem_empty[as]);
+        else mbar_arrive_cluster(&tmem_empty[as], 0);
+      }
       as ^= 1;
       if (as == 0) aphase ^= 1;
     }
   }
 
   tc_fence_before();
-  __syncthreads();
+  if constexpr (CG == 2) cluster_sync_all();
+  else __syncthreads();
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+    if constexpr (CG == 2) tmem_dealloc_pair<Cfg::kTmemCols>(tmem_base);
+    else tmem_dealloc<Cfg::kTmemCols>(tmem_base);
   }
 }
 
