@@ -145,16 +145,25 @@ class ShardedFrameStore:
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
 
     def search(self, queries, k):
-        import torch.distributed as dist
         s, i = self.local.search(queries, k)
         if self.world == 1:
             return s, i
-        Q, kk = s.shape
-        if kk < k:  # shard smaller than k: pad so every rank contributes the same shape
-            s = torch.cat([s, torch.full((Q, k - kk), float("-inf"), device=s.device)], 1)
-            i = torch.cat([i, torch.full((Q, k - kk), -1, dtype=torch.int64, device=i.device)], 1)
-        all_s = torch.empty((self.world, Q, k), dtype=torch.float32, device=s.device)
-        all_i = torch.empty((self.world, Q, k), dtype=torch.int64, device=s.device)
-        dist.all_gather_into_tensor(all_s, s.contiguous(), group=self.group)
-        dist.all_gather_into_tensor(all_i, i.contiguous(), group=self.group)
+        all_s, all_i = exchange_topk(s, i, k, self.world, self.group)
         return merge_topk(all_s, all_i)
+
+
+def exchange_topk(s, i, k, world, group=None):
+    """The one exchange step of the sharded search: every rank's (scores [Q, k'], idx [Q, k']) list, padded to k
+    with (-inf, -1) when its shard holds fewer than k rows, is all-gathered into [P, Q, k] on every rank
+    (NCCL over NVLink on the GPUs; the same code runs under gloo in tests/test_sharded_gloo.py)."""
+    import torch.distributed as dist
+    Q, kk = s.shape
+    if kk < k:
+        s = torch.cat([s, torch.full((Q, k - kk), float("-inf"), dtype=s.dtype, device=s.device)], 1)
+        i = torch.cat([i, torch.full((Q, k - kk), -1, dtype=torch.int64, device=i.device)], 1)
+    all_s = torch.empty((world, Q, k), dtype=torch.float32, device=s.device)
+    all_i = torch.empty((world, Q, k), dtype=torch.int64, device=s.device)
+    # output viewed as the dim-0 concatenation [P*Q, k] of the rank inputs (the form every backend accepts)
+    dist.all_gather_into_tensor(all_s.view(world * Q, k), s.contiguous(), group=group)
+    dist.all_gather_into_tensor(all_i.view(world * Q, k), i.contiguous(), group=group)
+    return all_s, all_i

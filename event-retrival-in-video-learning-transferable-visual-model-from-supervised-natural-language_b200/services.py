@@ -1,0 +1,443 @@
+"""Host-side mirror of the reference's service layer for the retrieval hot path.
+
+`EmbeddingService` keeps the reference's names, positional orders, defaults, return types and error behaviour
+(Backend/services/embedding_service.py:70-536) but every arithmetic step runs in libevr.so on the B200:
+  encode_image                    -> vit.VisionEncoder (through the `clip` face, clip.py)
+  load + L2 normalise (:208-210)  -> search.FrameStore.from_numpy  (evr_store_prepare, HBM-resident fp16 store)
+  np.dot + argsort (:314-320)     -> FrameStore.search             (evr_topk_search)
+  np.dot(emb[i:i+1], q.T) (:274)  -> FrameStore.rescore            (evr_rescore)
+The constructor takes the reference's own CacheService / PathService / DataService objects unchanged (they are
+stdlib-only); `PathService`, `CacheService`, `DataService` below are small mirrors of exactly the methods this
+path calls (path_service.py:47-93, cache_service.py:23-175, data_service.py:24-55) for standalone use.
+Quirks of the reference that are fixed rather than copied are listed in INTEGRATION.md.
+"""
+import json
+import os
+import threading
+import time
+
+import numpy as np
+import torch
+
+from . import clip as _clip
+from .search import FrameStore
+
+IMAGE_EXT = ('.jpg', '.jpeg', '.png')  # embedding_service.py:452
+
+
+class PathService:
+    """path_service.py:6-111 -- video_mapping.json lookup; `None` / unknown video -> first mapping entry."""
+
+    def __init__(self, base_dir, metadata_dir, embedding_dir):
+        self.base_dir, self.metadata_dir, self.embedding_dir = base_dir, metadata_dir, embedding_dir
+        self.video_data_mapping = self._load_video_data_mapping()
+
+    def _mapping_file(self):
+        return os.path.join(self.metadata_dir, "video_mapping.json")
+
+    def _load_video_data_mapping(self):
+        if os.path.exists(self._mapping_file()):
+            with open(self._mapping_file(), 'r', encoding='utf-8') as f:
+                return json.load(f)
+        return {}
+
+    def save_video_data_mapping(self):
+        with open(self._mapping_file(), 'w', encoding='utf-8') as f:
+            json.dump(self.video_data_mapping, f, ensure_ascii=False, indent=4)
+
+    def _entry(self, video_name, field, fallback):
+        m = self.video_data_mapping
+        if video_name and video_name in m:
+            return os.path.normpath(m[video_name][field])
+        if m:
+            return m[next(iter(m))][field]
+        return fallback
+
+    def get_metadata_path(self, video_name=None):
+        return self._entry(video_name, "metadata_file", os.path.join(self.metadata_dir, "output_samples.json"))
+
+    def get_embeddings_path(self, video_name=None):
+        return self._entry(video_name, "embeddings_file", os.path.join(self.embedding_dir, "image_embeddings.npy"))
+
+    def add_video_mapping(self, video_name, metadata_file, embeddings_file, video_path, frames_dir):
+        self.video_data_mapping[video_name] = {"metadata_file": metadata_file, "embeddings_file": embeddings_file,
+                                               "video_path": video_path, "frames_dir": frames_dir}
+
+
+class CacheService:
+    """cache_service.py:7-241 -- keyed in-memory caches with a TTL (default 3600 s); same key construction."""
+
+    def __init__(self, default_ttl=3600):
+        self.default_ttl = default_ttl
+        self._data = {}
+        self._lock = threading.Lock()
+
+    def _get(self, key):
+        with self._lock:
+            hit = self._data.get(key)
+            if hit is None:
+                return None
+            value, created, ttl = hit
+            if time.time() - created > ttl:
+                del self._data[key]
+                return None
+            return value
+
+    def _set(self, key, value, ttl=None):
+        with self._lock:
+            self._data[key] = (value, time.time(), self.default_ttl if ttl is None else ttl)
+
+    def get_path_cache(self, video_name):
+        return self._get(("paths", f"paths_{video_name or 'default'}"))
+
+    def set_path_cache(self, video_name, embeddings_path, json_path, ttl=None):
+        self._set(("paths", f"paths_{video_name or 'default'}"),
+                  {'embeddings_path': embeddings_path, 'json_path': json_path}, ttl)
+
+    def get_text_features(self, query, video_name):
+        return self._get(("text", f"{query}_{video_name or 'default'}"))
+
+    def set_text_features(self, query, video_name, features, ttl=None):
+        self._set(("text", f"{query}_{video_name or 'default'}"), features, ttl)
+
+    def get_embeddings(self, embeddings_path):
+        return self._get(("emb", embeddings_path))
+
+    def set_embeddings(self, embeddings_path, embeddings, ttl=None):
+        self._set(("emb", embeddings_path), embeddings, ttl)
+
+    def get_frames_list(self, json_path):
+        return self._get(("frames", json_path))
+
+    def set_frames_list(self, json_path, frames_list, ttl=None):
+        self._set(("frames", json_path), frames_list, ttl)
+
+    def get_search_results(self, query, video_name):
+        return self._get(("search", f"{query}_{video_name or 'default'}"))
+
+    def set_search_results(self, query, video_name, results, ttl=None):
+        self._set(("search", f"{query}_{video_name or 'default'}"), results, ttl)
+
+    def clear_all_caches(self):
+        with self._lock:
+            self._data.clear()
+
+
+class DataService:
+    """data_service.py:24-55 -- row i of the store <-> basename(metadata[i]["filepath"])."""
+
+    def __init__(self, path_service, cache_service):
+        self.path_service, self.cache_service = path_service, cache_service
+
+    def load_frames_from_json(self, video_name=None):
+        json_path = self.path_service.get_metadata_path(video_name)
+        frames = self.cache_service.get_frames_list(json_path)
+        if frames:
+            return frames
+        json_path = os.path.normpath(json_path)
+        try:
+            with open(json_path, 'r', encoding='utf-8') as f:
+                samples = json.load(f)
+            frames = [os.path.basename(s["filepath"]) for s in samples if "filepath" in s]
+            self.cache_service.set_frames_list(json_path, frames)
+            return frames
+        except Exception as e:  # the reference swallows and returns []
+            print(f"Error loading frames from JSON: {e}, path: {json_path}")
+            return []
+
+
+class EmbeddingService:
+    """Drop-in for Backend/services/embedding_service.py:EmbeddingService (same constructor positionals).
+
+    Extra keyword arguments (all optional, absent in the reference): `clip_module` (defaults to this package's
+    `clip`), `model_name`, `load_kwargs` (forwarded to clip.load, e.g. state_dict= / random_init=),
+    `text_encoder` (callable str -> [1, D] array, used while the text tower is not built: SURVEY 8f row 1),
+    `checkpoint_path` (fine-tuned CLIPWithClassifier checkpoint, embedding_service.py:93)."""
+
+    def __init__(self, cache_service, path_service, data_service, device="cuda", clip_module=None,
+                 model_name="ViT-B/32", load_kwargs=None, text_encoder=None, checkpoint_path=None):
+        self.cache_service, self.path_service, self.data_service = cache_service, path_service, data_service
+        self.device = device
+        self._clip = clip_module or _clip
+        self._model_name = model_name
+        self._load_kwargs = dict(load_kwargs or {})
+        self.text_encoder = text_encoder
+        self.original_model, self.preprocess = self._clip.load(model_name, device=device, **self._load_kwargs)
+        self.finetuned_model = None
+        self.active_model = "original"
+        self.checkpoint_path = checkpoint_path
+        self._stores = {}              # embeddings_path -> (mtime, FrameStore, source dtype)
+        self._lock = threading.RLock()  # the Flask dev server is threaded (app.py:968); the reference holds no locks
+        if checkpoint_path and os.path.exists(checkpoint_path):
+            try:
+                self._load_finetuned_model(checkpoint_path)
+            except Exception as e:
+                print(f"Error loading fine-tuned model: {e}")
+
+    # ---- models (a6) ------------------------------------------------------------------------------
+    def _load_finetuned_model(self, checkpoint_path):
+        """embedding_service.py:103-120: CLIPWithClassifier checkpoint, CLIP weights under `clip_model.`; at serve
+        time only encode_image + L2 normalise of that wrapper is used (:36-49), the classifier head is not."""
+        model, _ = self._clip.load(checkpoint_path, device=self.device)
+        self.finetuned_model = _FinetunedImageEncoder(model)
+
+    def set_active_model(self, model_name):
+        if model_name == "original":
+            self.active_model = "original"
+            return True
+        if model_name == "finetuned":
+            if self.finetuned_model is not None:
+                self.active_model = "finetuned"
+                return True
+            print("Fine-tuned model is not loaded!")
+            return False
+        print(f"Unknown model name: {model_name}")
+        return False
+
+    def get_active_model_name(self):
+        return self.active_model
+
+    def _encode_images(self, batch, model_key=None):
+        """-> numpy [B, D] un-normalised, in the model dtype (original) / unit-norm fp32 (fine-tuned wrapper)."""
+        key = model_key or self.active_model
+        with torch.no_grad():
+            if key == "finetuned" and self.finetuned_model is not None:
+                return self.finetuned_model(batch).cpu().numpy()
+            return self.original_model.encode_image(batch).cpu().numpy()
+
+    # ---- text features (a8) -----------------------------------------------------------------------
+    def get_text_features(self, query, video_name=None):
+        cache_key = f"{self.active_model}_{query}_{video_name or 'default'}"
+        features = self.cache_service.get_text_features(cache_key, video_name)
+        if features is not None:
+            return features
+        if self.text_encoder is not None:
+            features = np.asarray(self.text_encoder(query), dtype=np.float32).reshape(1, -1)
+        else:
+            model = self.original_model
+            if self.active_model == "finetuned" and self.finetuned_model is not None:
+                model = self.finetuned_model.clip_model
+            text_input = self._clip.tokenize([query]).to(self.device)
+            with torch.no_grad():
+                features = model.encode_text(text_input).cpu().numpy()
+        features = features / np.linalg.norm(features, axis=-1, keepdims=True)
+        self.cache_service.set_text_features(cache_key, video_name, features)
+        return features
+
+    # ---- store (a7) -------------------------------------------------------------------------------
+    def _frame_store(self, video_name=None):
+        """HBM-resident FrameStore of the video's `.npy` (re-read when the file changes); None if missing."""
+        path = self.path_service.get_embeddings_path(video_name)
+        if not os.path.exists(path):
+            print(f"Warning: Embeddings file not found: {path}")
+            return None, path
+        mtime = os.path.getmtime(path)
+        with self._lock:
+            hit = self._stores.get(path)
+            if hit is not None and hit[0] == mtime:
+                return hit, path
+            raw = np.load(path)
+            entry = (mtime, FrameStore.from_numpy(raw, device=self.device), raw.dtype)
+            self._stores[path] = entry
+            return entry, path
+
+    def get_embeddings(self, video_name=None):
+        """Unit-norm rows as a numpy array of the file's dtype (embedding_service.py:186-217).  The rows are the
+        device store read back (normalised by evr_store_prepare, fp16 in HBM), not a host re-computation."""
+        try:
+            entry, path = self._frame_store(video_name)
+            if entry is None:
+                return None
+            cached = self.cache_service.get_embeddings(path)
+            if cached is not None and len(cached) == entry[1].N:
+                return cached
+            emb = entry[1].rows.cpu().numpy().astype(entry[2] if entry[2] in (np.float16, np.float32)
+                                                     else np.float32, copy=False)
+            self.cache_service.set_embeddings(path, emb)
+            return emb
+        except Exception as e:
+            print(f"Error loading embeddings: {e}")
+            return None
+
+    def _frames(self, video_name):
+        json_path = self.path_service.get_metadata_path(video_name)
+        frames = self.cache_service.get_frames_list(json_path)
+        if frames is None:
+            frames = self.data_service.load_frames_from_json(video_name)
+            self.cache_service.set_frames_list(json_path, frames)
+        return frames
+
+    # ---- re-score (a11) ---------------------------------------------------------------------------
+    def extract_query_confidence(self, frame_path, query, video_name=None):
+        """cosine(frame row, text features) as a python float; 0.0 on a miss or any error (:219-282)."""
+        try:
+            text_features = self.get_text_features(query, video_name)
+            entry, _ = self._frame_store(video_name)
+            if entry is None:
+                return 0.0
+            index = self._row_index(video_name).get(frame_path)
+            if index is None:
+                index = self._row_index(video_name).get(os.path.basename(frame_path))
+            if index is None or index >= entry[1].N:
+                return 0.0
+            q = torch.from_numpy(np.ascontiguousarray(text_features, dtype=np.float32).reshape(-1))
+            return float(entry[1].rescore(q, [index]).item())
+        except Exception as e:
+            print(f"Error extracting query confidence: {e}")
+            return 0.0
+
+    def _row_index(self, video_name):
+        """frame name -> first row with that name: what `frames.index(name)` (:264) finds, without its O(N) walk."""
+        json_path = self.path_service.get_metadata_path(video_name)
+        frames = self._frames(video_name)
+        with self._lock:
+            hit = getattr(self, "_row_maps", {}).get(json_path)
+            if hit is not None and hit[0] is frames:
+                return hit[1]
+            table = {}
+            for i, f in enumerate(frames):
+                table.setdefault(f, i)
+                table.setdefault(os.path.basename(f), i)
+            self._row_maps = dict(getattr(self, "_row_maps", {}))
+            self._row_maps[json_path] = (frames, table)
+            return table
+
+    # ---- the scan (a9, a10) -----------------------------------------------------------------------
+    def search_with_scores(self, features, top_k, video_name=None):
+        """[(frame name, cosine)] in descending score: the pairs the reference builds at :330-333 before it drops
+        the scores.  `features` [1, D] / [D] unit-norm query."""
+        entry, _ = self._frame_store(video_name)
+        if entry is None:
+            return []
+        store = entry[1]
+        q = torch.from_numpy(np.ascontiguousarray(np.asarray(features, dtype=np.float32).reshape(1, -1)))
+        scores, idx = store.search(q, min(int(top_k), store.N))
+        scores, idx = scores[0].cpu().numpy(), idx[0].cpu().numpy()
+        frames = self._frames(video_name)
+        return [(frames[int(i)], float(s)) for i, s in zip(idx, scores)]
+
+    def search_top_frames(self, query, top_k, video_name=None):
+        """list of frame file names, best first; [] on any error; memoised like the reference (:284-344)."""
+        try:
+            cache_key = f"search_{self.active_model}_{query}_{top_k}"
+            cached = self.cache_service.get_search_results(cache_key, video_name)
+            if cached is not None:
+                return cached
+            text_features = self.get_text_features(query, video_name)
+            top_frames = [f for f, _ in self.search_with_scores(text_features, top_k, video_name)]
+            if top_frames or self._frame_store(video_name)[0] is not None:
+                self.cache_service.set_search_results(cache_key, video_name, top_frames)
+            return top_frames
+        except Exception as e:
+            print(f"Error in search_top_frames: {e}")
+            return []
+
+    def search_top_frames_by_image(self, image_features, top_k, video_name=None):
+        """Same scan with a given [1, D] query vector, no result cache (:346-392)."""
+        try:
+            return [f for f, _ in self.search_with_scores(image_features, top_k, video_name)]
+        except Exception as e:
+            print(f"Error in search_top_frames_by_image: {e}")
+            return []
+
+    # ---- encode (a2, a5) --------------------------------------------------------------------------
+    def extract_image_embedding(self, image_path):
+        """[1, D] unit-norm numpy embedding of one image file, None on error (:394-423)."""
+        try:
+            from PIL import Image
+            image = self.preprocess(Image.open(image_path)).unsqueeze(0).to(self.device)
+            emb = self._encode_images(image)
+            return emb / np.linalg.norm(emb, axis=-1, keepdims=True)
+        except Exception as e:
+            print(f"Error extracting embedding from {image_path}: {e}")
+            return None
+
+    def extract_and_save_embeddings_from_folder(self, folder_path, model_name=None, video_name=None):
+        """Encode every frame of a folder (sorted file names) and write `<video>_embeddings.npy` [N, D] unit-norm
+        (:425-536).  Returns the path, or None when the folder has no images.  Differences from the reference, all
+        from SURVEY.md 8g: the model is chosen per call without flipping `active_model` under other threads; an
+        unknown video gets `<embedding_dir>/<video>_embeddings.npy` instead of overwriting the first video's file;
+        an undecodable frame becomes a zero row (not a NameError / NaN row)."""
+        from PIL import Image
+        key = self.active_model
+        if model_name:
+            key = "original" if (model_name == "finetuned" and self.finetuned_model is None) else model_name
+            if key not in ("original", "finetuned"):
+                print(f"Unknown model name: {model_name}")
+                key = self.active_model
+        mapping = getattr(self.path_service, "video_data_mapping", {})
+        if video_name and video_name not in mapping and getattr(self.path_service, "embedding_dir", None):
+            embeddings_path = os.path.join(self.path_service.embedding_dir, f"{video_name}_embeddings.npy")
+        else:
+            embeddings_path = self.path_service.get_embeddings_path(video_name)
+        os.makedirs(os.path.dirname(embeddings_path) or ".", exist_ok=True)
+        frame_files = sorted(f for f in os.listdir(folder_path) if f.endswith(IMAGE_EXT))
+        if not frame_files:
+            print(f"No image files found in {folder_path}")
+            return None
+        S = self.original_model.visual.input_resolution
+        batch_size = 32  # :461
+        all_embeddings, bad_rows = [], []
+        for i in range(0, len(frame_files), batch_size):
+            batch = []
+            for j, name in enumerate(frame_files[i:i + batch_size]):
+                try:
+                    batch.append(self.preprocess(Image.open(os.path.join(folder_path, name)).convert('RGB')))
+                except Exception as e:
+                    print(f"Error preprocessing image {name}: {e}")
+                    batch.append(torch.zeros(3, S, S))
+                    bad_rows.append(i + j)
+            all_embeddings.append(self._encode_images(torch.stack(batch).to(self.device), key))
+        embeddings = np.vstack(all_embeddings)
+        norm = np.linalg.norm(embeddings, axis=-1, keepdims=True)
+        embeddings = embeddings / np.where(norm > 1e-8, norm, 1).astype(embeddings.dtype)
+        embeddings[bad_rows] = 0
+        np.save(embeddings_path, embeddings)
+        self._stamp_metadata(video_name, key)
+        return embeddings_path
+
+    def _stamp_metadata(self, video_name, model_key):
+        """:509-526 -- record which model produced the store in the video's metadata JSON."""
+        metadata_path = self.path_service.get_metadata_path(video_name)
+        mapping = getattr(self.path_service, "video_data_mapping", {})
+        if (video_name and video_name not in mapping) or not os.path.exists(metadata_path):
+            return
+        try:
+            with open(metadata_path, 'r', encoding='utf-8') as f:
+                metadata = json.load(f)
+            if isinstance(metadata, list):
+                for item in metadata:
+                    item['embedding_model'] = model_key
+            elif isinstance(metadata, dict):
+                metadata['embedding_model'] = model_key
+            with open(metadata_path, 'w', encoding='utf-8') as f:
+                json.dump(metadata, f, ensure_ascii=False, indent=2)
+        except Exception as e:
+            print(f"Error updating metadata with model info: {e}")
+
+
+class _FinetunedImageEncoder:
+    """Serve-time behaviour of CLIPWithClassifier.forward(images) (embedding_service.py:36-49): encode_image in
+    fp32, then L2 normalise.  (The classifier head is never evaluated on this path.)"""
+
+    def __init__(self, clip_model):
+        self.clip_model = clip_model.float()
+
+    def __call__(self, images, texts=None, get_embeddings=False):
+        f = self.clip_model.encode_image(images.float()).float()
+        return f / f.norm(dim=-1, keepdim=True)
+
+    def eval(self):
+        return self
+
+
+def initialize_services(base_dir, metadata_dir, embedding_dir, finetuned_model_path=None, **embedding_kwargs):
+    """services/__init__.py:11-64 for the services on this path (no SearchService / visualisation)."""
+    path_service = PathService(base_dir, metadata_dir, embedding_dir)
+    cache_service = CacheService()
+    data_service = DataService(path_service, cache_service)
+    embedding_service = EmbeddingService(cache_service, path_service, data_service, "cuda",
+                                         checkpoint_path=finetuned_model_path, **embedding_kwargs)
+    return {'path_service': path_service, 'cache_service': cache_service, 'data_service': data_service,
+            'embedding_service': embedding_service, 'search_service': None, 'device': "cuda",
+            'services_loaded': True}
