@@ -1,0 +1,190 @@
+"""Drop-in surface on the GPU: the reference's call sequence (ingest -> get_embeddings -> search_top_frames ->
+extract_query_confidence) through `services.EmbeddingService` / `clip` / `embedding`, checked against the oracle.
+
+Tolerances: encode cosine >= 0.999 per row vs the fp32 oracle; search ranks identical up to ties within 2^-10.
+"""
+import importlib
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import PKG
+from oracle import search_oracle as so
+from oracle import vit_oracle as vo
+
+pytestmark = pytest.mark.gpu
+EPS = 2.0 ** -10
+
+
+@pytest.fixture(scope="module")
+def visual():
+    return vo.build_visual("ViT-B/32", seed=1)
+
+
+@pytest.fixture(scope="module")
+def full_sd(visual):
+    sd = {"visual." + k: v for k, v in visual.state_dict().items()}
+    sd["logit_scale"] = torch.tensor(2.6592)
+    return sd
+
+
+def _write_frames(folder, names, seed=0, size=(256, 320)):
+    from PIL import Image
+    rng = np.random.default_rng(seed)
+    os.makedirs(folder, exist_ok=True)
+    for n in names:
+        # smooth random images survive PNG exactly and resize without aliasing surprises
+        low = rng.integers(0, 255, (8, 10, 3), dtype=np.uint8)
+        Image.fromarray(low).resize((size[1], size[0]), Image.BICUBIC).save(os.path.join(folder, n))
+
+
+def _site(tmp_path, full_sd, videos, text_encoder=None):
+    services = importlib.import_module(PKG + ".services")
+    meta, emb = tmp_path / "metadata", tmp_path / "embedding"
+    meta.mkdir(exist_ok=True)
+    emb.mkdir(exist_ok=True)
+    mapping = {}
+    for v, names in videos.items():
+        frames_dir = tmp_path / "frames" / v
+        _write_frames(str(frames_dir), names, seed=sum(map(ord, v)))
+        items = [{"filepath": str(frames_dir / n), "frameidx": int(os.path.splitext(n)[0])} for n in sorted(names)]
+        (meta / f"{v}_metadata.json").write_text(json.dumps(items))
+        mapping[v] = {"metadata_file": str(meta / f"{v}_metadata.json"),
+                      "embeddings_file": str(emb / f"{v}_embeddings.npy"),
+                      "video_path": "", "frames_dir": str(frames_dir)}
+    (meta / "video_mapping.json").write_text(json.dumps(mapping))
+    ps = services.PathService(str(tmp_path / "frames"), str(meta), str(emb))
+    cs = services.CacheService()
+    ds = services.DataService(ps, cs)
+    svc = services.EmbeddingService(cs, ps, ds, "cuda", load_kwargs=dict(state_dict=full_sd, max_batch=64),
+                                    text_encoder=text_encoder)
+    return svc, ps
+
+
+def _oracle_rows(visual, svc, folder, names):
+    from PIL import Image
+    pix = torch.stack([svc.preprocess(Image.open(os.path.join(folder, n)).convert("RGB")) for n in names])
+    return vo.encode_image(visual, pix, normalise=True)
+
+
+def test_ingest_writes_reference_layout(tmp_path, cuda, visual, full_sd):
+    names = [f"{i}.png" for i in (10074, 1061, 7, 300, 25, 42, 9000)] + ["notes.txt"]
+    svc, ps = _site(tmp_path, full_sd, {"vid": [n for n in names if n.endswith(".png")]})
+    folder = ps.video_data_mapping["vid"]["frames_dir"]
+    open(os.path.join(folder, "notes.txt"), "w").write("not an image")
+    path = svc.extract_and_save_embeddings_from_folder(folder, None, "vid")
+    assert path == ps.get_embeddings_path("vid") and os.path.exists(path)
+    out = np.load(path)
+    order = sorted(n for n in names if n.endswith(".png"))  # lexicographic: 10074 < 1061 < 25 ...
+    assert order[:2] == ["10074.png", "1061.png"]
+    assert out.shape == (7, 512) and out.dtype in (np.float16, np.float32) and out.flags["C_CONTIGUOUS"]
+    assert np.allclose(np.linalg.norm(out.astype(np.float32), axis=-1), 1.0, atol=2e-3)
+    ref = _oracle_rows(visual, svc, folder, order)
+    cos = (out.astype(np.float32) * ref).sum(-1) / np.linalg.norm(out.astype(np.float32), axis=-1)
+    assert cos.min() >= 0.999, cos
+    meta = json.load(open(ps.get_metadata_path("vid")))
+    assert all(item["embedding_model"] == "original" for item in meta)
+    assert svc.get_active_model_name() == "original"
+
+
+def test_ingest_edge_cases(tmp_path, cuda, full_sd):
+    svc, ps = _site(tmp_path, full_sd, {"vid": ["1.png", "2.png", "3.png"]})
+    empty = tmp_path / "empty"
+    empty.mkdir()
+    assert svc.extract_and_save_embeddings_from_folder(str(empty), None, "vid") is None
+    folder = ps.video_data_mapping["vid"]["frames_dir"]
+    open(os.path.join(folder, "2.png"), "wb").write(b"broken")  # undecodable frame -> zero row, no NaN
+    out = np.load(svc.extract_and_save_embeddings_from_folder(folder, "finetuned", "vid"))  # falls back to original
+    assert np.isfinite(out).all() and np.all(out[1] == 0) and np.all(np.abs(out[[0, 2]]).sum(-1) > 0)
+    # a video that is not in the mapping yet gets its own file instead of overwriting the default store (8g)
+    new = np.load(svc.extract_and_save_embeddings_from_folder(folder, None, "fresh"))
+    assert os.path.exists(os.path.join(ps.embedding_dir, "fresh_embeddings.npy")) and new.shape == (3, 512)
+    assert svc.extract_image_embedding(os.path.join(folder, "2.png")) is None
+    one = svc.extract_image_embedding(os.path.join(folder, "1.png"))
+    assert one.shape == (1, 512) and abs(np.linalg.norm(one.astype(np.float32)) - 1) < 2e-3
+    assert np.allclose(one.astype(np.float32)[0], out[0].astype(np.float32), atol=4e-3)
+
+
+def test_search_calls_match_oracle(tmp_path, cuda, full_sd):
+    rng = np.random.default_rng(3)
+    table = {}
+
+    def text_encoder(query):
+        if query not in table:
+            table[query] = rng.standard_normal((1, 512)).astype(np.float32)
+        return table[query]
+
+    names = [f"{i}.png" for i in range(3)]
+    svc, ps = _site(tmp_path, full_sd, {"first": names, "second": names}, text_encoder)
+    # the stores: un-normalised fp32 (first / default) and fp16 (second), 500 rows each, metadata to match
+    stores = {}
+    for v, dt in (("first", np.float32), ("second", np.float16)):
+        raw = (rng.standard_normal((500, 512)) * 3).astype(dt)
+        np.save(ps.get_embeddings_path(v), raw)
+        items = [{"filepath": f"/x/{v}/{i}.jpg", "frameidx": i} for i in range(500)]
+        json.dump(items, open(ps.get_metadata_path(v), "w"))
+        stores[v] = raw
+    for video, key in ((None, "first"), ("second", "second"), ("unknown", "first")):
+        emb = svc.get_embeddings(video)
+        ref_emb = so.normalise_store(stores[key])
+        assert emb.shape == (500, 512) and emb.dtype == stores[key].dtype
+        assert np.allclose(emb.astype(np.float32), ref_emb.astype(np.float32), atol=2 * EPS)
+        for query in ("a person running", "xe máy"):
+            q = svc.get_text_features(query, video)
+            assert q.shape == (1, 512) and abs(np.linalg.norm(q) - 1) < 1e-5
+            got = svc.search_top_frames(query, 30, video)
+            pairs = svc.search_with_scores(q, 30, video)
+            assert got == [f for f, _ in pairs] and len(got) == 30
+            ref_i, ref_s = so.batched_topk(ref_emb.astype(np.float32), q, 30)
+            got_i = np.array([int(os.path.splitext(f)[0]) for f in got])
+            assert so.topk_equal_up_to_ties(got_i, np.array([s for _, s in pairs]), ref_i[0], ref_s[0], 2 * EPS)
+            assert svc.search_top_frames(query, 30, video) is got          # memoised (:298, :339)
+            assert svc.search_top_frames_by_image(q, 30, video) == got
+            conf = svc.extract_query_confidence(got[0], query, video)
+            assert isinstance(conf, float)
+            assert abs(conf - so.query_confidence(ref_emb.astype(np.float32), int(got_i[0]), q)) < 2 * EPS
+            assert abs(svc.extract_query_confidence("/some/dir/" + got[3], query, video) - pairs[3][1]) < 1e-5
+            assert svc.extract_query_confidence("nope.jpg", query, video) == 0.0
+    assert len(svc.search_top_frames("k larger than the store", 5000, None)) == 500
+
+
+def test_errors_become_empty_results(tmp_path, cuda, full_sd):
+    svc, ps = _site(tmp_path, full_sd, {"vid": ["1.png"]})   # no .npy written, no text tower, no text_encoder
+    assert svc.get_embeddings("vid") is None
+    assert svc.search_top_frames("anything", 10, "vid") == []
+    assert svc.search_top_frames_by_image(np.ones((1, 512), np.float32), 10, "vid") == []
+    assert svc.extract_query_confidence("1.png", "anything", "vid") == 0.0
+    assert svc.set_active_model("finetuned") is False and svc.set_active_model("bogus") is False
+    assert svc.set_active_model("original") is True
+
+
+def test_clip_face_and_legacy_ingest(tmp_path, cuda, visual, full_sd):
+    clip = importlib.import_module(PKG + ".clip")
+    legacy = importlib.import_module(PKG + ".embedding")
+    model, preprocess = clip.load("ViT-B/32", device="cuda", state_dict=full_sd, max_batch=8)
+    assert model.visual.output_dim == 512 and model.dtype == torch.float16 and model.eval() is model
+    _, pix = vo.synthetic_frames(20, seed=4)          # 20 > max_batch: encode_image chunks internally
+    ref = vo.encode_image(visual, pix, normalise=False)
+    out = model.encode_image(pix.to(cuda))
+    assert out.dtype == torch.float16 and out.shape == (20, 512) and out.is_cuda
+    out32 = model.float().encode_image(pix.to(cuda))
+    assert out32.dtype == torch.float32
+    o, r = out32.cpu().numpy(), ref
+    cos = (o * r).sum(-1) / (np.linalg.norm(o, axis=-1) * np.linalg.norm(r, axis=-1))
+    assert cos.min() >= 0.999
+    assert np.allclose(np.linalg.norm(o, axis=-1), np.linalg.norm(r, axis=-1), rtol=2e-2)  # un-normalised, as clip
+    with pytest.raises(NotImplementedError):
+        model.encode_text(torch.zeros((1, 77), dtype=torch.long))
+    # legacy entry point: un-normalised rows in the model dtype, `<video>_embeddings.npy`, os.walk order
+    folder = tmp_path / "clip_7"
+    _write_frames(str(folder), ["b.png", "a.jpg", "c.JPEG"], seed=9)
+    (folder / "skip.txt").write_text("x")
+    path = legacy.extract_and_save_embeddings_from_folder(
+        str(folder), "ViT-B/32", embeddings_dir=str(tmp_path / "emb"), load_kwargs=dict(state_dict=full_sd))
+    assert os.path.basename(path) == "clip_7_embeddings.npy"
+    rows = np.load(path)
+    assert rows.shape == (3, 512) and rows.dtype == np.float16
+    assert np.linalg.norm(rows.astype(np.float32), axis=-1).min() > 2.0   # not normalised (embedding.py:55)
