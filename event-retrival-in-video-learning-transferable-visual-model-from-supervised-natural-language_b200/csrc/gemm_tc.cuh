@@ -3,11 +3,11 @@
 // replaces the nn.Linear / nn.Conv2d(patch) / `x @ proj` library GEMMs issued by
 // openai/CLIP clip/model.py VisionTransformer.forward (SURVEY.md 2.2 K1,K4,K6-K9).
 //
-// One CTA per SM, 256 threads:
+// One CTA per SM, 384 threads:
 //   warp 0  : TMA producer   (one elected lane)   global -> 128B-swizzled smem ring
 //   warp 1  : MMA issuer     (one elected lane)   tcgen05.mma kind::f16, fp32 accumulators in TMEM
 //   warp 2  : TMEM allocator
-//   warp 4-7: epilogue       tcgen05.ld -> registers -> fused bias/QuickGELU/residual -> global
+//   warp 4-11: epilogue      tcgen05.ld -> registers -> fused bias/QuickGELU/residual -> staged, coalesced global
 // Two TMEM accumulator stages let the epilogue of tile i overlap the MMAs of tile i+1.
 #pragma once
 #include <cuda_bf16.h>
@@ -36,21 +36,21 @@ struct GemmArgs {
 
 constexpr int kGemmBlockM = 128;
 constexpr int kGemmBlockK = 64;  // 64 x 16-bit = one 128-B swizzle atom row
-constexpr int kGemmThreads = 256;
+constexpr int kGemmThreads = 384;  // 4 control warps + 8 epilogue warps
 
-// Epilogue staging: every epilogue warp owns a [32 rows x 64 columns] tile in shared memory (row pitch padded by 16 B
+// Epilogue staging: every epilogue warp owns a [32 rows x 32 columns] tile in shared memory (row pitch padded by 16 B
 // so the row-per-lane writes are bank-conflict free).  TMEM hands each lane one accumulator ROW; staging turns that
-// into row-contiguous, fully coalesced 16-B global accesses (4 or 2 whole rows of 128/256 B per warp instruction).
-constexpr int kEpiCols = 64;
+// into row-contiguous, fully coalesced 16-B global accesses (8 or 4 row segments of 64/128 B per warp instruction).
+constexpr int kEpiCols = 32;
 template <int EPI>
 struct EpiCfg {
   static constexpr bool kOutBf16 = (EPI == 0 || EPI == 1);
   static constexpr int kElt = kOutBf16 ? 2 : 4;
-  static constexpr int kRowBytes = kEpiCols * kElt;       // 128 | 256
-  static constexpr int kPitch = kRowBytes + 16;           // 144 | 272
+  static constexpr int kRowBytes = kEpiCols * kElt;       // 64 | 128
+  static constexpr int kPitch = kRowBytes + 16;           // 80 | 144
   static constexpr int kWarpBytes = 32 * kPitch;
-  static constexpr int kBytes = 4 * kWarpBytes;           // 18 432 | 34 816
-  static constexpr int kUnitsPerRow = kRowBytes / 16;     // 8 | 16
+  static constexpr int kBytes = 8 * kWarpBytes;           // 20 480 | 36 864
+  static constexpr int kUnitsPerRow = kRowBytes / 16;     // 4 | 8
 };
 
 // CG = 1: one CTA per 128 x BLOCK_N tile.  CG = 2: a CTA pair (cta_group::2) per 256 x BLOCK_N tile; each CTA stages its
@@ -129,7 +129,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tmem_full[i], 1);
-      mbar_init(&tmem_empty[i], 4 * CG);  // one arrive per epilogue warp of the unit
+      mbar_init(&tmem_empty[i], 8 * CG);  // one arrive per epilogue warp of the unit
     }
     fence_barrier_init();
   }
@@ -206,34 +206,65 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       }
     }
   } else if (warp >= 4) {
-    // ===== epilogue: warp q owns TMEM lanes [32q, 32q+32) = rows [32q, 32q+32) of the tile =====
-    const int q = warp - 4;
-    uint8_t* stage = smem_epi + q * Epi::kWarpBytes;
+    // ===== epilogue: 8 warps.  Warp w reads TMEM lanes [32 (w%4), +32) = 32 rows of the tile (the hardware's lane
+    // quarter rule); the two warps of a quarter split every 64-column group into its two 32-column halves, so each
+    // SM sub-partition has two epilogue warps to hide tcgen05.ld / shared / global latency behind each other.
+    const int ew = warp - 4;
+    const int q = ew & 3;
+    const int hsel = ew >> 2;
+    constexpr int kChunks = BLOCK_N / 64;  // 32-column chunks per warp
+    uint8_t* stage = smem_epi + ew * Epi::kWarpBytes;
     uint8_t* my_row = stage + lane * Epi::kPitch;
+    constexpr int kColsPerUnit = 16 / Epi::kElt;
+    constexpr int kIters = Epi::kUnitsPerRow;  // 16-B units per lane per chunk: 4 (bf16) | 8 (fp32)
     int as = 0;
     uint32_t aphase = 0;
     for (int tile = unit; tile < num_tiles; tile += num_units) {
       const int m_idx = tile % num_m, n_idx = tile / num_m;
+      const int row0 = m_idx * kTileM + static_cast<int>(rank) * kGemmBlockM + q * 32;  // first row of this warp
+      const int col_base = n_idx * BLOCK_N + hsel * kEpiCols;
+      // residual stream values of a chunk: independent of the MMAs, so they are fetched ahead of the accumulators
+      // (first chunk before the accumulator barrier, chunk c+1 before the stores of chunk c)
+      float4 old[2][EPI == EPI_F32_RESID ? kIters : 1];
+      auto load_resid = [&](float4* dst, int col0) {
+#pragma unroll
+        for (int i = 0; i < kIters; ++i) {
+          const int u = i * 32 + lane;
+          const int r = u / Epi::kUnitsPerRow, cu = u % Epi::kUnitsPerRow;
+          const int row = row0 + r, col = col0 + cu * kColsPerUnit;
+          dst[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (row < args.M && col < args.N)
+            dst[i] = __ldcg(reinterpret_cast<const float4*>(static_cast<const float*>(args.out) +
+                                                            static_cast<size_t>(row) * args.ldo + col));
+        }
+      };
+      if constexpr (EPI == EPI_F32_RESID) load_resid(old[0], col_base);
       mbar_wait(&tmem_full[as], aphase);
       tc_fence_after();
-      const int row0 = m_idx * kTileM + static_cast<int>(rank) * kGemmBlockM + q * 32;  // first row of this warp
-#pragma unroll 1
-      for (int c = 0; c < BLOCK_N / kEpiCols; ++c) {
-        const int col0 = n_idx * BLOCK_N + c * kEpiCols;
-        if (col0 >= args.N) break;  // warp-uniform
-        // ---- accumulator row of this lane: 64 columns, + bias (+ QuickGELU), into the staging tile
-        uint32_t v[2][32];
-        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BLOCK_N + c * kEpiCols;
-        tmem_ld_32x32(taddr, v[0]);
-        tmem_ld_32x32(taddr + 32, v[1]);
-        tmem_ld_wait();
+      uint32_t v[2][32];
+      const uint32_t taddr0 = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BLOCK_N + hsel * kEpiCols;
+      tmem_ld_32x32(taddr0, v[0]);
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
+      for (int c = 0; c < kChunks; ++c) {
+        const int col0 = col_base + c * 64;
+        tmem_ld_wait();
+        if (c + 1 < kChunks) {
+          tmem_ld_32x32(taddr0 + (c + 1) * 64, v[(c + 1) & 1]);
+        } else {
+          // every accumulator value of this warp is in registers: hand the TMEM stage back to the MMA issuer
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) {
+            if (leader) mbar_arrive(&tmem_empty[as]);
+            else mbar_arrive_cluster(&tmem_empty[as], 0);
+          }
+        }
+        if (col0 < args.N) {  // warp-uniform (N is a multiple of 32)
           float f[32];
 #pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[h][j]);
-          if (args.bias != nullptr && col0 + h * 32 < args.N) {
-            const float4* b4 = reinterpret_cast<const float4*>(args.bias + col0 + h * 32);
+          for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[c & 1][j]);
+          if (args.bias != nullptr) {
+            const float4* b4 = reinterpret_cast<const float4*>(args.bias + col0);
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
               const float4 bb = __ldg(b4 + j);
@@ -245,7 +276,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             for (int j = 0; j < 32; ++j) f[j] = quick_gelu(f[j]);
           }
           if constexpr (Epi::kOutBf16) {
-            uint4* o = reinterpret_cast<uint4*>(my_row + h * 64);
+            uint4* o = reinterpret_cast<uint4*>(my_row);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
               uint4 w;
@@ -256,45 +287,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
               o[j] = w;
             }
           } else {
-            float4* o = reinterpret_cast<float4*>(my_row + h * 128);
+            float4* o = reinterpret_cast<float4*>(my_row);
 #pragma unroll
             for (int j = 0; j < 8; ++j) o[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
           }
-        }
-        __syncwarp();
-        // ---- coalesced copy-out: 16-B units, consecutive lanes walk along a row
-        constexpr int kUnits = 32 * Epi::kUnitsPerRow;
-        constexpr int kColsPerUnit = 16 / Epi::kElt;
-        constexpr int kIters = kUnits / 32;  // 8 (bf16) | 16 (fp32)
-        if constexpr (EPI == EPI_F32_RESID) {
-          // read-modify-write of the fp32 residual stream: all loads of a batch are issued before the first store
-          // (the compiler cannot reorder them itself: the accesses are in place)
-#pragma unroll
-          for (int half = 0; half < 2; ++half) {
-            float4 old[kIters / 2];
-#pragma unroll
-            for (int i = 0; i < kIters / 2; ++i) {
-              const int u = (half * (kIters / 2) + i) * 32 + lane;
-              const int r = u / Epi::kUnitsPerRow, cu = u % Epi::kUnitsPerRow;
-              const int row = row0 + r, col = col0 + cu * kColsPerUnit;
-              old[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-              if (row < args.M && col < args.N)
-                old[i] = __ldcg(reinterpret_cast<const float4*>(static_cast<const float*>(args.out) +
-                                                                static_cast<size_t>(row) * args.ldo + col));
-            }
-#pragma unroll
-            for (int i = 0; i < kIters / 2; ++i) {
-              const int u = (half * (kIters / 2) + i) * 32 + lane;
-              const int r = u / Epi::kUnitsPerRow, cu = u % Epi::kUnitsPerRow;
-              const int row = row0 + r, col = col0 + cu * kColsPerUnit;
-              if (row < args.M && col < args.N) {
-                float4 x = *reinterpret_cast<const float4*>(stage + r * Epi::kPitch + cu * 16);
-                x.x += old[i].x; x.y += old[i].y; x.z += old[i].z; x.w += old[i].w;
-                *reinterpret_cast<float4*>(static_cast<float*>(args.out) + static_cast<size_t>(row) * args.ldo + col) = x;
-              }
-            }
+          __syncwarp();
+          if constexpr (EPI == EPI_F32_RESID) {
+            if (c + 1 < kChunks) load_resid(old[(c + 1) & 1], col0 + 64);
           }
-        } else {
+          // ---- coalesced copy-out: 16-B units, consecutive lanes walk along a row
 #pragma unroll
           for (int it = 0; it < kIters; ++it) {
             const int u = it * 32 + lane;
@@ -307,6 +308,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
               } else {
                 float4 x = *reinterpret_cast<const float4*>(&sv);
                 size_t out_row = row;
+                if constexpr (EPI == EPI_F32_RESID) {
+                  const float4 o4 = old[c & 1][it];
+                  x.x += o4.x; x.y += o4.y; x.z += o4.z; x.w += o4.w;
+                }
                 if constexpr (EPI == EPI_PATCH) {
                   const int bimg = row / args.patches, pp = row - bimg * args.patches;
                   out_row = static_cast<size_t>(bimg) * (args.patches + 1) + 1 + pp;
@@ -317,14 +322,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
               }
             }
           }
+          __syncwarp();  // the staging tile is rewritten by the next chunk
         }
-        __syncwarp();  // the staging tile is rewritten by the next chunk
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) {
-        if (leader) mbar_arrive(&tmem_empty[as]);
-        else mbar_arrive_cluster(&tmem_empty[as], 0);
       }
       as ^= 1;
       if (as == 0) aphase ^= 1;
