@@ -149,7 +149,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = unit; tile < num_tiles; tile += num_units) {
-        const int m_idx = tile % num_m, n_idx = tile / num_m;
+        const int n_idx = tile % num_n, m_idx = tile / num_n;  // n-fast: the N tiles of one row block run together, A is read from HBM once
         const int a_row = m_idx * kTileM + static_cast<int>(rank) * kGemmBlockM;
         const int b_row = n_idx * BLOCK_N + static_cast<int>(rank) * Cfg::kBRows;
         for (int kb = 0; kb < num_kb; ++kb) {
@@ -220,7 +220,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     int as = 0;
     uint32_t aphase = 0;
     for (int tile = unit; tile < num_tiles; tile += num_units) {
-      const int m_idx = tile % num_m, n_idx = tile / num_m;
+      const int n_idx = tile % num_n, m_idx = tile / num_n;  // n-fast: the N tiles of one row block run together, A is read from HBM once
       const int row0 = m_idx * kTileM + static_cast<int>(rank) * kGemmBlockM + q * 32;  // first row of this warp
       const int col_base = n_idx * BLOCK_N + hsel * kEpiCols;
       // residual stream values of a chunk: independent of the MMAs, so they are fetched ahead of the accumulators
