@@ -27,7 +27,23 @@ struct evr_vit {
   // workspaces (owned)
   __nv_bfloat16 *a0 = nullptr, *hbuf = nullptr, *qkv = nullptr, *attn = nullptr, *fbuf = nullptr, *cls_ln = nullptr;
   float *x = nullptr, *emb = nullptr;
+  // L2 residency of the fp32 residual stream (touched 4x per layer, between which ~180 MB of activations stream by)
+  size_t l2_persist = 0, l2_window_max = 0;
 };
+
+// Pins the residual stream `x` in L2 for the kernels that follow on `s` (access-policy window: hits persist, the rest of
+// the traffic streams past it); bytes == 0 removes the window.  Best effort: a refusal only costs bandwidth.
+static void set_residual_window(const evr_vit* h, size_t bytes, cudaStream_t s) {
+  if (h->l2_persist == 0) return;
+  cudaStreamAttrValue v{};
+  if (bytes > h->l2_window_max) bytes = h->l2_window_max;
+  v.accessPolicyWindow.base_ptr = bytes ? h->x : nullptr;
+  v.accessPolicyWindow.num_bytes = bytes;
+  v.accessPolicyWindow.hitRatio = bytes > h->l2_persist ? static_cast<float>(h->l2_persist) / bytes : 1.0f;
+  v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+  v.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+  if (cudaStreamSetAttribute(s, cudaStreamAttributeAccessPolicyWindow, &v) != cudaSuccess) cudaGetLastError();
+}
 
 static int copy_f32(float*& cursor, const void* src, size_t n, const float** dst, cudaStream_t s) {
   EVR_CHECK_CUDA(cudaMemcpyAsync(cursor, src, n * sizeof(float), cudaMemcpyDeviceToDevice, s));
@@ -117,6 +133,20 @@ extern "C" int evr_vit_create(const evr_vit_cfg* cfg, const void* const* w, int 
   EVR_CHECK_CUDA(cudaMalloc(&h->fbuf, rows * 4 * d * 2));
   EVR_CHECK_CUDA(cudaMalloc(&h->cls_ln, static_cast<size_t>(max_batch) * d * 2));
   EVR_CHECK_CUDA(cudaMalloc(&h->emb, static_cast<size_t>(max_batch) * od * 4));
+  {
+    int dev = 0, max_persist = 0, max_window = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, dev);
+    cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, dev);
+    size_t want = rows * d * 4;
+    if (want > static_cast<size_t>(max_persist)) want = max_persist;
+    if (want > 0 && max_window > 0 && cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want) == cudaSuccess) {
+      h->l2_persist = want;
+      h->l2_window_max = max_window;
+    } else {
+      cudaGetLastError();
+    }
+  }
   EVR_CHECK_CUDA(cudaStreamSynchronize(s));
   *out = h;
   return 0;
@@ -143,6 +173,7 @@ static int encode_chunk(evr_vit* h, const void* pixels, int pix_dtype, int B, vo
                         int l2_normalise, cudaStream_t s) {
   const int d = h->cfg.width, L = h->L, P = h->g * h->g, od = h->cfg.out_dim;
   const int M = B * L;
+  set_residual_window(h, static_cast<size_t>(M) * d * sizeof(float), s);
   // K1/K2: patch embed (+pos) and class rows
   if (launch_im2col(pixels, pix_dtype, B, h->cfg.image_size, h->cfg.patch, h->K0p, h->a0, s)) return 1;
   if (gemm(h->a0, h->K0p, h->w_conv, h->K0p, B * P, d, nullptr, h->x, d, EPI_PATCH, s, h->pos, P)) return 1;
@@ -162,6 +193,7 @@ static int encode_chunk(evr_vit* h, const void* pixels, int pix_dtype, int B, vo
   if (launch_layernorm(h->x, static_cast<size_t>(L) * d, h->cls_ln, d, 1, h->ln_post_g, h->ln_post_b, B, d, s)) return 1;
   if (gemm(h->cls_ln, d, h->w_projT, d, B, od, nullptr, h->emb, od, EPI_F32, s)) return 1;
   if (launch_l2norm_cast(h->emb, out, out_dtype, B, od, l2_normalise, s)) return 1;
+  set_residual_window(h, 0, s);
   return 0;
 }
 
