@@ -57,8 +57,10 @@ static int choose_block_n(int M, int N, int units, int tile_m) {
   for (int bn : cands) {
     const int tiles = num_m * ((N + bn - 1) / bn);
     const int rounds = (tiles + units - 1) / units;
-    // time per tile ~ BLOCK_N; narrow tiles move more operand bytes per FLOP
-    double cost = static_cast<double>(rounds) * bn * (bn == 128 ? 1.06 : 1.0);
+    // time per tile and k-block: the larger of the MMA time (~ tile_m * bn) and the operand delivery time (~ tile_m + bn
+    // rows of 128 B through L2 -> SM at the measured ~9.5 TB/s: 1.45 clk per row against 2 clk per 256 x 1 of MMA)
+    const double mma = 2.0 * bn * tile_m / 256.0, feed = 1.45 * (tile_m + bn);
+    double cost = static_cast<double>(rounds) * (mma > feed ? mma : feed);
     if (cost < best_cost) { best_cost = cost; best = bn; }
   }
   return best;

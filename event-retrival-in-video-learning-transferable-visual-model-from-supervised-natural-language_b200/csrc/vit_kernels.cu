@@ -134,7 +134,7 @@ int launch_layernorm(const float* in, size_t in_stride, void* out, size_t out_st
 }
 
 // ----------------------------------------------------------------------------- attention core
-// One CTA per (head, image); K and V^T of the head staged in shared memory; each warp owns 16-query
+// One CTA per (head, image); K and V of the head staged in shared memory (V read with ldmatrix.trans); each warp owns 16-query
 // tiles and runs a flash-style loop over 64-key blocks with mma.sync.m16n8k16 (bf16 in, fp32 acc).
 // The whole sequence (50 or 257 tokens) is far below one tcgen05 tile, and the core is ~1 % of the
 // tower's FLOPs, so it stays on the warp-level MMA path; no attention mask (vision tower).
@@ -156,9 +156,9 @@ attention_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restric
   extern __shared__ __align__(16) uint8_t attn_smem[];
   const int h = blockIdx.x, b = blockIdx.y;
   const int Lp = (L + 63) & ~63;
-  const int vstride = Lp + 8;
   __nv_bfloat16* Ks = reinterpret_cast<__nv_bfloat16*>(attn_smem);  // [Lp][72]
-  __nv_bfloat16* Vt = Ks + Lp * kAttnKStride;                       // [64][Lp + 8]
+  __nv_bfloat16* Vs = Ks + Lp * kAttnKStride;                       // [Lp][72]  (row-major; the P.V operand is read
+                                                                    //  with ldmatrix.trans, no transposed copy)
   const size_t row0 = static_cast<size_t>(b) * L;
   const int ld = 3 * d;
 
@@ -171,9 +171,7 @@ attention_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restric
       vv = *reinterpret_cast<const uint4*>(base + 2 * d);
     }
     *reinterpret_cast<uint4*>(Ks + r * kAttnKStride + c * 8) = kv;
-    const __nv_bfloat16* ve = reinterpret_cast<const __nv_bfloat16*>(&vv);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) Vt[(c * 8 + j) * vstride + r] = ve[j];
+    *reinterpret_cast<uint4*>(Vs + r * kAttnKStride + c * 8) = vv;
   }
   __syncthreads();
 
@@ -249,11 +247,18 @@ attention_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restric
         pa[2] = pack2_bf16(s[2 * kk + 1][0], s[2 * kk + 1][1]);
         pa[3] = pack2_bf16(s[2 * kk + 1][2], s[2 * kk + 1][3]);
 #pragma unroll
-        for (int nt = 0; nt < 8; ++nt) {
-          const __nv_bfloat16* vr = Vt + (nt * 8 + g) * vstride + kb * 64 + 16 * kk + 2 * t;
-          const uint32_t b0 = *reinterpret_cast<const uint32_t*>(vr);
-          const uint32_t b1 = *reinterpret_cast<const uint32_t*>(vr + 8);
+        for (int nt = 0; nt < 8; nt += 2) {
+          // four 8x8 blocks of V: (keys 16kk + {0,8}) x (dims 8nt + {0,8}); lane l addresses row l%8 of block l/8.
+          // .trans hands thread (g,t) the pairs V[key 2t, 2t+1][dim g] = the col-major B fragment of m16n8k16.
+          const int blk = lane >> 3;
+          const __nv_bfloat16* vr = Vs + (kb * 64 + 16 * kk + (blk & 1) * 8 + (lane & 7)) * kAttnKStride +
+                                    (nt + (blk >> 1)) * 8;
+          uint32_t b0, b1, b2, b3;
+          asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+                       : "=r"(b0), "=r"(b1), "=r"(b2), "=r"(b3)
+                       : "r"(static_cast<uint32_t>(__cvta_generic_to_shared(vr))));
           mma_bf16_16816(o[nt], pa, b0, b1);
+          mma_bf16_16816(o[nt + 1], pa, b2, b3);
         }
       }
     }
@@ -281,7 +286,7 @@ int launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L,
                      cudaStream_t stream) {
   EVR_REQUIRE(heads * 64 == d, "attention: head dim must be 64 (d=%d heads=%d)", d, heads);
   const int Lp = (L + 63) & ~63;
-  const size_t smem = static_cast<size_t>(Lp) * kAttnKStride * 2 + 64 * static_cast<size_t>(Lp + 8) * 2;
+  const size_t smem = 2 * static_cast<size_t>(Lp) * kAttnKStride * 2;  // K and V, [Lp][72] bf16 each
   EVR_REQUIRE(smem <= 200 * 1024, "attention: sequence %d too long for the single-CTA K/V staging", L);
   static size_t configured = 0;
   if (smem > 48 * 1024 && smem > configured) {
