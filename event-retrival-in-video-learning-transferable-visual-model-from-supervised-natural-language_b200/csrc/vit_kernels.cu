@@ -282,9 +282,177 @@ attention_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restric
   }
 }
 
+// ---- short sequences (L <= 64: ViT-B/32 has 50 tokens): persistent CTAs, double-buffered cp.async staging ----------
+// The one-item-per-CTA kernel above is latency-bound at L = 50 (every CTA pays its global round trips with 16 warps
+// per SM resident: ncu long_scoreboard 5.1 of 6.4 stall cycles per issue).  Here a CTA walks a strided list of
+// (image, head) items; Q, K, V of item i+1 stream into the second shared-memory stage with cp.async while item i is
+// computed, all MMA fragments come from shared memory through ldmatrix, and O leaves through shared memory as whole
+// 128-byte rows.  One key block, so the softmax is a single pass.
+constexpr int kAttnTileBytes = 64 * kAttnKStride * 2;   // one [64][72] bf16 tile
+constexpr int kAttnStageBytes = 3 * kAttnTileBytes;     // Q, K, V
+
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst))),
+               "l"(gsrc)
+               : "memory");
+}
+__device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], const void* smem_src) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(static_cast<uint32_t>(__cvta_generic_to_shared(smem_src))));
+}
+__device__ __forceinline__ void ldmatrix_x4_trans(uint32_t (&r)[4], const void* smem_src) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(static_cast<uint32_t>(__cvta_generic_to_shared(smem_src))));
+}
+
+__global__ void __launch_bounds__(128)
+attention_short_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, int L, int d, int heads,
+                       int items, float scale_log2e) {
+  extern __shared__ __align__(16) uint8_t attn_smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const int ld = 3 * d;
+  // rows >= L of both stages are never written by the loader: zero them once
+  for (int i = threadIdx.x; i < 2 * 3 * (64 - L) * 9; i += 128) {
+    const int tile = i / ((64 - L) * 9), rem = i % ((64 - L) * 9);
+    *reinterpret_cast<uint4*>(attn_smem + tile * kAttnTileBytes + (L + rem / 9) * (kAttnKStride * 2) + (rem % 9) * 16) =
+        make_uint4(0, 0, 0, 0);
+  }
+  auto prefetch = [&](int item, int stage) {
+    const int b = item / heads, h = item - b * heads;
+    const __nv_bfloat16* src = qkv + static_cast<size_t>(b) * L * ld + h * 64;
+    uint8_t* dst = attn_smem + stage * kAttnStageBytes;
+    for (int i = threadIdx.x; i < 3 * L * 8; i += 128) {   // 16-B chunks: (tile, row, chunk)
+      const int tile = i / (L * 8), rem = i - tile * (L * 8), r = rem >> 3, c = rem & 7;
+      cp_async16(dst + tile * kAttnTileBytes + r * (kAttnKStride * 2) + c * 16,
+                 src + static_cast<size_t>(r) * ld + tile * d + c * 8);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+
+  int item = blockIdx.x, stage = 0;
+  if (item < items) prefetch(item, 0);
+  for (; item < items; item += gridDim.x, stage ^= 1) {
+    const int next = item + gridDim.x;
+    if (next < items) {
+      prefetch(next, stage ^ 1);
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+    __syncthreads();
+    __nv_bfloat16* Qs = reinterpret_cast<__nv_bfloat16*>(attn_smem + stage * kAttnStageBytes);
+    const __nv_bfloat16* Ks = Qs + 64 * kAttnKStride;
+    const __nv_bfloat16* Vs = Ks + 64 * kAttnKStride;
+    const int m0 = warp * 16;  // this warp's 16 query rows
+    if (m0 < L) {
+      uint32_t qa[4][4];
+#pragma unroll
+      for (int kk = 0; kk < 4; ++kk)
+        ldmatrix_x4(qa[kk], Qs + (m0 + (lane & 7) + ((lane >> 3) & 1) * 8) * kAttnKStride + 16 * kk + (lane >> 4) * 8);
+      float s[8][4];
+#pragma unroll
+      for (int nt = 0; nt < 8; nt += 2) {
+        s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+        s[nt + 1][0] = s[nt + 1][1] = s[nt + 1][2] = s[nt + 1][3] = 0.f;
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+          uint32_t kb[4];  // K[key 8nt + g][dims 16kk + {0,8} + 2t..] for key tiles nt, nt+1
+          ldmatrix_x4(kb, Ks + ((nt + (lane >> 4)) * 8 + (lane & 7)) * kAttnKStride + 16 * kk + ((lane >> 3) & 1) * 8);
+          mma_bf16_16816(s[nt], qa[kk], kb[0], kb[1]);
+          mma_bf16_16816(s[nt + 1], qa[kk], kb[2], kb[3]);
+        }
+      }
+      float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        const int col = nt * 8 + 2 * t;
+        s[nt][0] = col < L ? s[nt][0] * scale_log2e : -INFINITY;
+        s[nt][1] = col + 1 < L ? s[nt][1] * scale_log2e : -INFINITY;
+        s[nt][2] = col < L ? s[nt][2] * scale_log2e : -INFINITY;
+        s[nt][3] = col + 1 < L ? s[nt][3] * scale_log2e : -INFINITY;
+        mx0 = fmaxf(mx0, fmaxf(s[nt][0], s[nt][1]));
+        mx1 = fmaxf(mx1, fmaxf(s[nt][2], s[nt][3]));
+      }
+      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+      float l0 = 0.f, l1 = 0.f;
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        s[nt][0] = exp2f(s[nt][0] - mx0);
+        s[nt][1] = exp2f(s[nt][1] - mx0);
+        s[nt][2] = exp2f(s[nt][2] - mx1);
+        s[nt][3] = exp2f(s[nt][3] - mx1);
+        l0 += s[nt][0] + s[nt][1];
+        l1 += s[nt][2] + s[nt][3];
+      }
+      float o[8][4];
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) { o[nt][0] = o[nt][1] = o[nt][2] = o[nt][3] = 0.f; }
+#pragma unroll
+      for (int kk = 0; kk < 4; ++kk) {
+        uint32_t pa[4];
+        pa[0] = pack2_bf16(s[2 * kk][0], s[2 * kk][1]);
+        pa[1] = pack2_bf16(s[2 * kk][2], s[2 * kk][3]);
+        pa[2] = pack2_bf16(s[2 * kk + 1][0], s[2 * kk + 1][1]);
+        pa[3] = pack2_bf16(s[2 * kk + 1][2], s[2 * kk + 1][3]);
+#pragma unroll
+        for (int nt = 0; nt < 8; nt += 2) {
+          uint32_t vb[4];
+          ldmatrix_x4_trans(vb, Vs + (16 * kk + ((lane >> 3) & 1) * 8 + (lane & 7)) * kAttnKStride + (nt + (lane >> 4)) * 8);
+          mma_bf16_16816(o[nt], pa, vb[0], vb[1]);
+          mma_bf16_16816(o[nt + 1], pa, vb[2], vb[3]);
+        }
+      }
+      l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+      l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+      l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+      l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+      const float i0 = 1.0f / l0, i1 = 1.0f / l1;
+      // O through this warp's own 16 rows of the Q tile (its Q fragments are in registers), then whole rows to global
+      __syncwarp();
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        *reinterpret_cast<uint32_t*>(Qs + (m0 + g) * kAttnKStride + nt * 8 + 2 * t) = pack2_bf16(o[nt][0] * i0, o[nt][1] * i0);
+        *reinterpret_cast<uint32_t*>(Qs + (m0 + g + 8) * kAttnKStride + nt * 8 + 2 * t) = pack2_bf16(o[nt][2] * i1, o[nt][3] * i1);
+      }
+      __syncwarp();
+      const int b = item / heads, h = item - b * heads;
+      __nv_bfloat16* obase = out + static_cast<size_t>(b) * L * d + h * 64;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int u = i * 32 + lane, r = m0 + (u >> 3), c = u & 7;
+        if (r < L)
+          *reinterpret_cast<uint4*>(obase + static_cast<size_t>(r) * d + c * 8) =
+              *reinterpret_cast<const uint4*>(Qs + r * kAttnKStride + c * 8);
+      }
+    }
+    __syncthreads();  // this stage is refilled by the prefetch issued at the top of the next iteration
+  }
+}
+
 int launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int d, int heads,
                      cudaStream_t stream) {
   EVR_REQUIRE(heads * 64 == d, "attention: head dim must be 64 (d=%d heads=%d)", d, heads);
+  if (L <= 64) {
+    static bool configured_short = false;
+    if (!configured_short) {
+      EVR_CHECK_CUDA(cudaFuncSetAttribute(attention_short_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          2 * kAttnStageBytes));
+      configured_short = true;
+    }
+    const int items = B * heads, slots = sm_count() * 4;        // 4 CTAs (2 x 27 KB stages each) per SM
+    const int per_cta = (items + slots - 1) / slots;
+    const int grid = (items + per_cta - 1) / per_cta;           // every CTA walks the same number of items (+-1)
+    ProfScope ps(PF_ATTN, stream);
+    attention_short_kernel<<<grid, 128, 2 * kAttnStageBytes, stream>>>(qkv, out, L, d, heads, items,
+                                                                       0.125f * 1.4426950408889634f);
+    EVR_CHECK_LAUNCH();
+    return 0;
+  }
   const int Lp = (L + 63) & ~63;
   const size_t smem = 2 * static_cast<size_t>(Lp) * kAttnKStride * 2;  // K and V, [Lp][72] bf16 each
   EVR_REQUIRE(smem <= 200 * 1024, "attention: sequence %d too long for the single-CTA K/V staging", L);
