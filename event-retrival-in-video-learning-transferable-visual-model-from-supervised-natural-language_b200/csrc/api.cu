@@ -3,6 +3,8 @@
 #include <vector>
 
 #include "../../include/evr.h"
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace evr {
@@ -63,6 +65,15 @@ int sm_count() {
     if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
   }
   return n;
+}
+
+bool pdl_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("EVR_NO_PDL");
+    on = (e && e[0] == '1') ? 0 : 1;
+  }
+  return on == 1;
 }
 
 // ---- per-family kernel timing ---------------------------------------------------------------------

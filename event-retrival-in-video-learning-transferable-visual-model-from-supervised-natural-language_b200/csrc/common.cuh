@@ -50,6 +50,32 @@ int make_tmap_2d_16b(CUtensorMap* out, const void* base, uint64_t rows, uint64_t
 
 int sm_count();
 
+// Programmatic dependent launch (PDL): kernels of one encode are launched with programmatic stream serialisation, so
+// a kernel's CTAs become resident -- and run their prologue (barrier init, TMEM allocation, descriptor prefetch) --
+// while the previous kernel drains; `pdl_wait()` blocks until that previous grid has completed and flushed its
+// writes.  Every kernel launched this way calls pdl_wait() before its first access to activations (which also keeps
+// completion transitive along the chain).  EVR_NO_PDL=1 turns the attribute off.
+bool pdl_enabled();
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+#endif
+
 // Optional per-kernel-family timing (bench.py's roofline leg): when enabled through evr_profile_enable(1), every
 // launch site brackets its kernel with a pair of CUDA events on the launching stream.  Off by default (no cost).
 enum ProfFamily : int {

@@ -14,6 +14,8 @@ __constant__ float c_clip_std[3] = {0.26862954f, 0.26130258f, 0.27577711f};
 __global__ void __launch_bounds__(256)
 im2col_kernel(const void* __restrict__ pixels, int pix_dtype, size_t total_pairs, int S, int p, int g, int K, int Kp,
               __nv_bfloat16* __restrict__ out) {
+  pdl_launch_dependents();
+  pdl_wait();
   const size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (idx >= total_pairs) return;
   const int half_k = K >> 1;
@@ -47,7 +49,7 @@ int launch_im2col(const void* pixels, int pix_dtype, int B, int S, int p, int Kp
   const size_t total = static_cast<size_t>(B) * g * g * (K / 2);
   const unsigned blocks = static_cast<unsigned>((total + 255) / 256);
   ProfScope ps(PF_VIT_MISC, stream);
-  im2col_kernel<<<blocks, 256, 0, stream>>>(pixels, pix_dtype, total, S, p, g, K, Kp, out);
+  EVR_CHECK_CUDA(launch_pdl(im2col_kernel, dim3(blocks), dim3(256), 0, stream, pixels, pix_dtype, total, S, p, g, K, Kp, out));
   EVR_CHECK_LAUNCH();
   return 0;
 }
@@ -55,13 +57,15 @@ int launch_im2col(const void* pixels, int pix_dtype, int B, int S, int p, int Kp
 // ----------------------------------------------------------------------------- cls rows
 __global__ void cls_rows_kernel(float* __restrict__ x, const float* __restrict__ cls, const float* __restrict__ pos,
                                 int L, int d) {
+  pdl_launch_dependents();
+  pdl_wait();
   float* row = x + static_cast<size_t>(blockIdx.x) * L * d;
   for (int i = threadIdx.x; i < d; i += blockDim.x) row[i] = cls[i] + pos[i];
 }
 
 int launch_cls_rows(float* x, const float* cls, const float* pos, int B, int L, int d, cudaStream_t stream) {
   ProfScope ps(PF_VIT_MISC, stream);
-  cls_rows_kernel<<<B, 256, 0, stream>>>(x, cls, pos, L, d);
+  EVR_CHECK_CUDA(launch_pdl(cls_rows_kernel, dim3(B), dim3(256), 0, stream, x, cls, pos, L, d));
   EVR_CHECK_LAUNCH();
   return 0;
 }
@@ -71,6 +75,8 @@ template <int D4, bool OUT_BF16>
 __global__ void __launch_bounds__(256)
 layernorm_kernel(const float* in, size_t in_stride, void* out, size_t out_stride,  // in may alias out (ln_pre)
                  const float* __restrict__ gamma, const float* __restrict__ beta, int rows) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * 8 + warp;
   if (row >= rows) return;
@@ -123,11 +129,11 @@ int launch_layernorm(const float* in, size_t in_stride, void* out, size_t out_st
   const int blocks = (rows + 7) / 8;
   ProfScope ps(PF_LN, stream);
   if (d == 768) {
-    if (out_bf16) layernorm_kernel<6, true><<<blocks, 256, 0, stream>>>(in, in_stride, out, out_stride, gamma, beta, rows);
-    else layernorm_kernel<6, false><<<blocks, 256, 0, stream>>>(in, in_stride, out, out_stride, gamma, beta, rows);
+    if (out_bf16) EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<6, true>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows));
+    else EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<6, false>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows));
   } else {
-    if (out_bf16) layernorm_kernel<8, true><<<blocks, 256, 0, stream>>>(in, in_stride, out, out_stride, gamma, beta, rows);
-    else layernorm_kernel<8, false><<<blocks, 256, 0, stream>>>(in, in_stride, out, out_stride, gamma, beta, rows);
+    if (out_bf16) EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<8, true>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows));
+    else EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<8, false>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows));
   }
   EVR_CHECK_LAUNCH();
   return 0;
@@ -153,6 +159,8 @@ constexpr int kAttnKStride = 72;  // bf16 elements per K row in smem (64 + 8 pad
 
 __global__ void __launch_bounds__(128)
 attention_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, int L, int d, float scale) {
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ __align__(16) uint8_t attn_smem[];
   const int h = blockIdx.x, b = blockIdx.y;
   const int Lp = (L + 63) & ~63;
@@ -310,6 +318,8 @@ __device__ __forceinline__ void ldmatrix_x4_trans(uint32_t (&r)[4], const void* 
 __global__ void __launch_bounds__(128)
 attention_short_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, int L, int d, int heads,
                        int items, float scale_log2e) {
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ __align__(16) uint8_t attn_smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const int ld = 3 * d;
@@ -448,8 +458,7 @@ int launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L,
     const int per_cta = (items + slots - 1) / slots;
     const int grid = (items + per_cta - 1) / per_cta;           // every CTA walks the same number of items (+-1)
     ProfScope ps(PF_ATTN, stream);
-    attention_short_kernel<<<grid, 128, 2 * kAttnStageBytes, stream>>>(qkv, out, L, d, heads, items,
-                                                                       0.125f * 1.4426950408889634f);
+    EVR_CHECK_CUDA(launch_pdl(attention_short_kernel, dim3(grid), dim3(128), 2 * kAttnStageBytes, stream, qkv, out, L, d, heads, items, 0.125f * 1.4426950408889634f));
     EVR_CHECK_LAUNCH();
     return 0;
   }
@@ -463,7 +472,7 @@ int launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L,
     configured = smem;
   }
   ProfScope ps(PF_ATTN, stream);
-  attention_kernel<<<dim3(heads, B), 128, smem, stream>>>(qkv, out, L, d, 0.125f);
+  EVR_CHECK_CUDA(launch_pdl(attention_kernel, dim3(dim3(heads, B)), dim3(128), smem, stream, qkv, out, L, d, 0.125f));
   EVR_CHECK_LAUNCH();
   return 0;
 }
@@ -472,6 +481,8 @@ int launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L,
 __global__ void __launch_bounds__(256)
 l2norm_cast_kernel(const float* __restrict__ in, void* __restrict__ out, int out_dtype, int rows, int D,
                    int normalise) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * 8 + warp;
   if (row >= rows) return;
@@ -494,7 +505,7 @@ l2norm_cast_kernel(const float* __restrict__ in, void* __restrict__ out, int out
 int launch_l2norm_cast(const float* in, void* out, int out_dtype, int rows, int D, int normalise,
                        cudaStream_t stream) {
   ProfScope ps(PF_VIT_MISC, stream);
-  l2norm_cast_kernel<<<(rows + 7) / 8, 256, 0, stream>>>(in, out, out_dtype, rows, D, normalise);
+  EVR_CHECK_CUDA(launch_pdl(l2norm_cast_kernel, dim3((rows + 7) / 8), dim3(256), 0, stream, in, out, out_dtype, rows, D, normalise));
   EVR_CHECK_LAUNCH();
   return 0;
 }

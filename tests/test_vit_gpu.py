@@ -140,3 +140,44 @@ def test_vit_argument_errors(pkg, cuda, b32):
     with pytest.raises(ValueError):
         enc.encode(torch.zeros((1, 224, 224, 4), dtype=torch.uint8, device=cuda))
     assert enc.encode(torch.zeros((0, 3, 224, 224), device=cuda)).shape == (0, 512)
+
+
+@pytest.mark.parametrize("name,n_img", [("ViT-B/32", 160), ("ViT-L/14", 12)])
+def test_retrieval_metrics_unchanged(pkg, cuda, name, n_img):
+    """BASELINE config 5 in small: encode -> index -> query, R@K / MRR by compare_models.py:1004-1090's definitions.
+    The metrics of the GPU embeddings must equal those of the fp32 oracle embeddings on the same synthetic frames and
+    captions (5 noisy copies of each oracle image embedding); a rank may move only where two similarities are closer
+    than the bf16 tower's error (random-init towers give embeddings with mean pairwise cosine 0.98, so gaps are small):
+    R@K may differ by max(2 captions, 0.01) and MRR by 0.01 (stated tolerance).  The t2i
+    ranks are also recomputed through the fused scan (FrameStore.search over the GPU-encoded store)."""
+    from oracle import search_oracle as so
+    visual = vo.build_visual(name, seed=3)
+    u8, pix = vo.synthetic_frames(n_img, seed=6)
+    ref = vo.encode_image(visual, pix, normalise=True)
+    enc = pkg.vit.VisionEncoder.from_state_dict(visual.state_dict(), name, device=cuda, max_batch=64)
+    emb_dev = enc.encode(pix.to(cuda), normalise=True)
+    emb = emb_dev.cpu().numpy()
+    assert _cos(emb, ref).min() >= MIN_COS
+    rng = np.random.default_rng(8)
+    caps = 5
+    # random-init towers give highly correlated image embeddings: the noise is scaled to the spread between them
+    spread = np.linalg.norm(ref - ref.mean(0), axis=-1).mean()
+    txt = np.repeat(ref, caps, axis=0) + rng.standard_normal((n_img * caps, ref.shape[1])).astype(np.float32) \
+        * (7.0 * spread / np.sqrt(ref.shape[1]))
+    txt /= np.linalg.norm(txt, axis=-1, keepdims=True)
+    m_ref, m_gpu = so.t2i_i2t_metrics(ref, txt, caps), so.t2i_i2t_metrics(emb, txt, caps)
+    assert 0.05 < m_ref["t2i"]["R@1"] < 1.0 or n_img < 20      # the task is not degenerate
+    for side, n in (("t2i", n_img * caps), ("i2t", n_img)):
+        for k in ("R@1", "R@5", "R@10"):
+            assert abs(m_ref[side][k] - m_gpu[side][k]) <= max(2.0 / n, 0.01) + 1e-9, (side, k, m_ref[side], m_gpu[side])
+        assert abs(m_ref[side]["MRR"] - m_gpu[side]["MRR"]) <= 0.01
+    # t2i through the product path: captions are the queries, the GPU-encoded frames are the store
+    store = pkg.search.FrameStore.from_tensor(emb_dev, device=cuda)
+    k = min(10, n_img)
+    sc, idx = store.search(torch.from_numpy(txt).to(cuda), k)
+    idx = idx.cpu().numpy()
+    gt = np.arange(n_img * caps) // caps
+    for kk in (1, 5, 10):
+        if kk <= k:
+            r_at_k = float(np.mean((idx[:, :kk] == gt[:, None]).any(1)))
+            assert abs(r_at_k - m_ref["t2i"][f"R@{kk}"]) <= max(2.0 / (n_img * caps), 0.01) + 1e-9, (kk, r_at_k, m_ref["t2i"])
