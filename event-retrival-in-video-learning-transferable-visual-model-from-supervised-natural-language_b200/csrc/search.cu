@@ -101,6 +101,7 @@ struct ScanArgs {
   int* counts;         // [num_slices][q_pad]       entries used in each list
   float* group_max;    // sample pass only (else nullptr): [q_pad][groups] max score of every 64-row group
   int groups;          // 64-row groups in the sample = N / 64
+  int stages;          // depth of the store-row smem ring actually used (<= kScanStages; 2 at D = 768)
 };
 
 // Warp-cooperative exact prune of one query's candidate list to its top-k.  All 32 lanes call with the
@@ -164,7 +165,8 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   const int q_bytes = kScanQTile * args.D * 2;
   uint8_t* smem_q = smem;                 // [num_kb][128 x 64] swizzled, resident
   uint8_t* smem_s = smem + q_bytes;       // [kScanStages][128 x 64]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_s + kScanStages * kScanStageBytes);
+  const int nst = args.stages;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_s + nst * kScanStageBytes);
   uint64_t* full_bar = bars;                                         // [kScanStages]
   uint64_t* empty_bar = bars + kScanStages;                          // [kScanStages]
   uint64_t* acc_full = bars + 2 * kScanStages;                       // [kAcc] (room for 4)
@@ -188,7 +190,7 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   }
   if (warp == 1 && lane == 0) {
     // full / q_full / acc_empty collect one arrival per CTA of the unit (the peer arrives remotely on the leader's)
-    for (int i = 0; i < kScanStages; ++i) { mbar_init(&full_bar[i], CG); mbar_init(&empty_bar[i], 1); }
+    for (int i = 0; i < nst; ++i) { mbar_init(&full_bar[i], CG); mbar_init(&empty_bar[i], 1); }
     for (int i = 0; i < kAcc; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4 * CG); }
     mbar_init(q_full, CG);
     mbar_init(q_empty, 1);
@@ -240,7 +242,7 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
               mbar_expect_tx(&full_bar[stage], kScanStageBytes);
               tma_load_2d(smem_s + stage * kScanStageBytes, &tmap_s, &full_bar[stage], kb * 64, row, row_policy);
             }
-            if (++stage == kScanStages) { stage = 0; phase ^= 1; }
+            if (++stage == nst) { stage = 0; phase ^= 1; }
           }
         }
       }
@@ -276,7 +278,7 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             }
             if constexpr (CG == 2) umma_commit_pair(&empty_bar[stage]);
             else umma_commit(&empty_bar[stage]);
-            if (++stage == kScanStages) { stage = 0; phase ^= 1; }
+            if (++stage == nst) { stage = 0; phase ^= 1; }
           }
           if constexpr (CG == 2) umma_commit_pair(&acc_full[as]);
           else umma_commit(&acc_full[as]);
@@ -738,7 +740,7 @@ static int64_t sample_rows(int64_t N, int k, int Q) {
 
 static int plan_scan(int64_t N, int D, int Q, int k, ScanPlan* p) {
   EVR_REQUIRE(N >= 1 && N < (int64_t(1) << 31) - 256, "top-k scan: N=%lld out of range", (long long)N);
-  EVR_REQUIRE(D % 64 == 0 && D >= 64 && D <= 512, "top-k scan: D=%d must be a multiple of 64 in [64, 512]", D);
+  EVR_REQUIRE(D % 64 == 0 && D >= 64 && D <= 768, "top-k scan: D=%d must be a multiple of 64 in [64, 768]", D);
   EVR_REQUIRE(Q >= 1, "top-k scan: Q=%d", Q);
   EVR_REQUIRE(k >= 1 && k <= kMaxFusedK, "top-k scan: k=%d must be in [1, %d]", k, kMaxFusedK);
   const int sms = sm_count();
@@ -838,7 +840,12 @@ static int run_scan(const ScanCore& c, const void* store, int64_t N, int D, cons
   CUtensorMap tq, ts;
   if (int r = make_tmap_2d_16b(&tq, queries, Q, D, static_cast<uint64_t>(D) * 2, kScanQTile, false)) return r;
   if (int r = make_tmap_2d_16b(&ts, store, N, D, static_cast<uint64_t>(D) * 2, kScanRowTile, false)) return r;
-  const int smem = kScanQTile * D * 2 + kScanStages * kScanStageBytes + 1024 + 256;
+  // the resident query tile takes 128 * D * 2 bytes; the ring gets what is left of the 227 KB (6 stages up to D = 512,
+  // 2 at D = 768: ViT-L/14 stores scan correctly, with a shallower pipeline)
+  int stages = (227 * 1024 - 1024 - 256 - kScanQTile * D * 2) / kScanStageBytes;
+  if (stages > kScanStages) stages = kScanStages;
+  a.stages = stages;
+  const int smem = kScanQTile * D * 2 + stages * kScanStageBytes + 1024 + 256;
   {
     ProfScope ps(PF_SCAN, s);
     int r;

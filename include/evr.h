@@ -39,7 +39,7 @@ int evr_store_prepare(const void* src, int src_dtype, int64_t N, int D, void* ds
 /* ---- fused cosine scan + top-k -------------------------------------------------------
  * replaces  np.dot(embeddings, q.T).flatten() ; np.argsort(sim)[::-1][:top_k]
  *           Backend/services/embedding_service.py:314-320 and :365-371
- * store   [N, D] fp16 (from evr_store_prepare), D % 64 == 0, D <= 512
+ * store   [N, D] fp16 (from evr_store_prepare), D % 64 == 0, D <= 768 (ViT-L/14); the row ring is 6 deep up to D = 512, 2 at 768
  * queries [Q, D] fp16
  * out_scores [Q, k] fp32 descending; out_idx [Q, k] int64 = row_offset + local row.
  * 1 <= k <= 1024.  If k > N the tail is filled with score -inf / idx -1.

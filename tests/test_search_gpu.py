@@ -63,12 +63,21 @@ def test_synthetic_vs_oracle(pkg, cuda, N, Q, k):
     _check(pkg, cuda, raw, q, k)
 
 
-@pytest.mark.parametrize("D", [64, 128, 256, 448])
+@pytest.mark.parametrize("D", [64, 128, 256, 448, 640, 768])
 def test_other_embedding_widths(pkg, cuda, D):
     rng = np.random.default_rng(D)
     raw = rng.standard_normal((3000, D)).astype(np.float32)
     q = _unit(rng.standard_normal((4, D)).astype(np.float32))
     _check(pkg, cuda, raw, q, 20)
+
+
+def test_vit_l14_width_large_store_and_query_batch(pkg, cuda):
+    """D = 768 (ViT-L/14 embeddings, BASELINE config 5): the shallower 2-stage row ring must still be exact, on the
+    one-CTA path (Q <= 128), on the CTA-pair path (Q > 128) and with the sample pre-pass (N >= 32768)."""
+    rng = np.random.default_rng(768)
+    raw = rng.standard_normal((40_000, 768)).astype(np.float32)
+    _check(pkg, cuda, raw, _unit(rng.standard_normal((3, 768)).astype(np.float32)), 100)
+    _check(pkg, cuda, raw[:9_000], _unit(rng.standard_normal((200, 768)).astype(np.float32)), 10)
 
 
 def test_fp16_unnormalised_store(pkg, cuda):
