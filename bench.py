@@ -35,6 +35,16 @@ VIT_NAME = "ViT-B/32"
 
 
 # ----------------------------------------------------------------------------------------------- helpers
+def ncu_traffic(kernel):
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture (profiles/traffic.json:
+    dram__bytes_read.sum + dram__bytes_write.sum averaged over the captured launches); None when there is no capture."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f)[kernel]["dram_bytes_per_launch"]
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -194,7 +204,7 @@ def bench_encode(pkg, vo, dev, rank, world, steps, warmup, batch, peaks):
         roof = {
             "bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05, all ViT GEMMs)",
             "achieved": round(achieved, 1), "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
-            "frac": round(achieved / peaks["tf_sustained"], 4), "traffic": None,
+            "frac": round(achieved / peaks["tf_sustained"], 4), "traffic": ncu_traffic("gemm_tc_kernel"),
             "peak_source": peaks["source"] + ", sustained bf16",
             "flops_per_launch_avg": gemm_flops * batch * steps / max(gemm_n, 1),
             "avg_launch_ms": round(gemm_ms / max(gemm_n, 1), 5),
@@ -304,7 +314,7 @@ def bench_search(pkg, dev, rank, world, steps, warmup, total_rows, Q, k, peaks):
             "peak": peaks["tf_sustained"] if tensor_bound else peaks["hbm_gbs"],
             "unit": "TFLOP/s" if tensor_bound else "GB/s",
             "frac": round((ach_tf / peaks["tf_sustained"]) if tensor_bound else (ach_gb / peaks["hbm_gbs"]), 4),
-            "traffic": None, "peak_source": peaks["source"], "avg_launch_ms": round(scan_ms, 4),
+            "traffic": ncu_traffic("topk_scan_kernel"), "peak_source": peaks["source"], "avg_launch_ms": round(scan_ms, 4),
             "launches_per_step": fam["topk_scan"][1] // steps, "achieved_gbs": round(ach_gb, 1), "achieved_tflops": round(ach_tf, 1),
             "share_of_step": round(fam["topk_scan"][0] / sum(v[0] for v in fam.values()), 4),
             "family_ms_per_step": {kk: round(v[0] / steps, 4) for kk, v in fam.items() if v[1]},

@@ -6,10 +6,11 @@ Drop-in mirror of the reference's Python surface for this path (SURVEY.md sectio
   services        -- `EmbeddingService`, `initialize_services` and the path/cache/data services it needs
   search          -- FrameStore: HBM-resident fp16 store + fused top-k (single GPU and row-sharded)
   vit             -- VisionEncoder: the hand-written tower behind `encode_image`
+  text            -- TextEncoder: the text tower behind `encode_text`; tokenizer: `clip.tokenize` (BPE restated)
 The CUDA library (lib/libevr.so, built by __graft_entry__.build()) is required; there is no CPU fallback.
 """
 from . import _lib  # noqa: F401  (fails loudly if libevr.so is missing)
-from . import search, vit  # noqa: F401
+from . import search, text, vit  # noqa: F401
 from . import clip, embedding, services  # noqa: F401
 
-__all__ = ["search", "vit", "clip", "embedding", "services", "_lib"]
+__all__ = ["search", "vit", "text", "clip", "embedding", "services", "_lib"]

@@ -25,6 +25,11 @@ class VitCfg(ctypes.Structure):
                 ("heads", c_int), ("out_dim", c_int)]
 
 
+class TextCfg(ctypes.Structure):
+    _fields_ = [("context_length", c_int), ("vocab_size", c_int), ("width", c_int), ("layers", c_int),
+                ("heads", c_int), ("out_dim", c_int)]
+
+
 # name -> (restype, argtypes); every symbol include/evr.h declares
 SIGNATURES = {
     "evr_last_error": (ctypes.c_char_p, []),
@@ -42,6 +47,10 @@ SIGNATURES = {
                                ctypes.POINTER(c_void_p)]),
     "evr_vit_destroy": (c_int, [c_void_p]),
     "evr_vit_encode": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_int, c_int, c_void_p]),
+    "evr_text_create": (c_int, [ctypes.POINTER(TextCfg), ctypes.POINTER(c_void_p), c_int, c_int,
+                                ctypes.POINTER(c_void_p)]),
+    "evr_text_destroy": (c_int, [c_void_p]),
+    "evr_text_encode": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_void_p]),
     "evr_gemm_bf16": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
 }
 for _name, (_res, _args) in SIGNATURES.items():

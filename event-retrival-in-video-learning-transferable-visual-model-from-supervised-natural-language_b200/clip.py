@@ -4,7 +4,7 @@ The reference does `import clip` (un-vendored submodule Backend/CLIP = openai/CL
   clip.load(name, device=..., jit=False) -> (model, preprocess)   embedding.py:22, embedding_service.py:86,106
   model.encode_image(Tensor[B,3,224,224]) -> Tensor[B,D]           embedding.py:49, embedding_service.py:41,414,490
   model.visual.output_dim, model.logit_scale, model.dtype, .float(), .eval(), .to()   embedding_service.py:22-34
-  clip.tokenize / model.encode_text                                 embedding_service.py:169-177
+  clip.tokenize / model.encode_text                                 embedding_service.py:169-177 (text.TextEncoder)
 `load` here returns a model whose `encode_image` runs the hand-written sm_100a tower (vit.VisionEncoder ->
 libevr.so).  Put this module on sys.path as `clip` and the reference's service code runs unchanged.
 
@@ -17,6 +17,7 @@ import os
 
 import torch
 
+from .text import TextEncoder, text_weight_keys
 from .vit import GEOMETRY, VisionEncoder, weight_keys
 
 CLIP_MEAN = (0.48145466, 0.4578275, 0.40821073)  # clip/clip.py _transform; compare_models.py:39
@@ -63,6 +64,39 @@ def random_visual_state_dict(name="ViT-B/32", seed=1):
     return full
 
 
+TEXT_GEOMETRY = {  # clip/model.py build_model: text half
+    "ViT-B/32": dict(width=512, layers=12, out_dim=512), "ViT-B/16": dict(width=512, layers=12, out_dim=512),
+    "ViT-L/14": dict(width=768, layers=12, out_dim=768),
+}
+
+
+def random_text_state_dict(name="ViT-B/32", seed=1, context_length=77, vocab_size=49408):
+    """Seeded random text-tower weights with openai's init scales (CLIP.initialize_parameters: token 0.02,
+    positional 0.01, attention d^-0.5, out/c_proj d^-0.5 (2 layers)^-0.5, c_fc (2d)^-0.5, text_projection d^-0.5)."""
+    g = TEXT_GEOMETRY[name]
+    d, layers, out = g["width"], g["layers"], g["out_dim"]
+    gen = torch.Generator().manual_seed(int(seed) + 7919)
+
+    def n(*shape, std):
+        return torch.randn(*shape, generator=gen) * std
+
+    s = d ** -0.5
+    sd = {"token_embedding.weight": n(vocab_size, d, std=0.02), "positional_embedding": n(context_length, d, std=0.01)}
+    for i in range(layers):
+        b = f"transformer.resblocks.{i}."
+        sd[b + "ln_1.weight"], sd[b + "ln_1.bias"] = torch.ones(d), torch.zeros(d)
+        sd[b + "attn.in_proj_weight"], sd[b + "attn.in_proj_bias"] = n(3 * d, d, std=s), torch.zeros(3 * d)
+        sd[b + "attn.out_proj.weight"] = n(d, d, std=s * (2 * layers) ** -0.5)
+        sd[b + "attn.out_proj.bias"] = torch.zeros(d)
+        sd[b + "ln_2.weight"], sd[b + "ln_2.bias"] = torch.ones(d), torch.zeros(d)
+        sd[b + "mlp.c_fc.weight"], sd[b + "mlp.c_fc.bias"] = n(4 * d, d, std=(2 * d) ** -0.5), torch.zeros(4 * d)
+        sd[b + "mlp.c_proj.weight"] = n(d, 4 * d, std=s * (2 * layers) ** -0.5)
+        sd[b + "mlp.c_proj.bias"] = torch.zeros(d)
+    sd["ln_final.weight"], sd["ln_final.bias"] = torch.ones(d), torch.zeros(d)
+    sd["text_projection"] = n(d, out, std=s)
+    return sd
+
+
 def _find_checkpoint(name, download_root):
     root = download_root or os.environ.get("EVR_CLIP_ROOT") or os.path.expanduser("~/.cache/clip")
     path = os.path.join(root, name.replace("/", "-") + ".pt")
@@ -104,7 +138,9 @@ class CLIPModel:
         if self.device.type != "cuda":
             raise RuntimeError("this CLIP runs on a CUDA device only (no CPU path); got device=%r" % (device,))
         self._sd = {k: v.detach().to("cpu", torch.float32) for k, v in state_dict.items()
-                    if k.startswith("visual.") or k == "logit_scale"}
+                    if torch.is_tensor(v) and v.is_floating_point()}
+        self._text = None
+        self._max_batch = max_batch
         enc = VisionEncoder.from_state_dict(self._sd, name, self.device, max_batch=max_batch, prefix="visual.")
         self.visual = _Visual(enc, name)
         self.logit_scale = self._sd.get("logit_scale", torch.tensor(2.6592)).to(self.device)
@@ -154,8 +190,18 @@ class CLIPModel:
             return torch.empty((0, self.visual.output_dim), dtype=self.dtype, device=self.device)
         return out[0] if len(out) == 1 else torch.cat(out, 0)
 
+    @property
+    def has_text_tower(self):
+        return "token_embedding.weight" in self._sd and "text_projection" in self._sd
+
+    @torch.no_grad()
     def encode_text(self, text):
-        raise NotImplementedError("encode_text: the text tower is SURVEY.md 8(f) row 1 (next), not built yet")
+        """LongTensor[B, 77] (clip.tokenize) -> [B, D] in the model dtype, on the sm_100a text tower."""
+        if not self.has_text_tower:
+            raise NotImplementedError("this checkpoint holds no text tower (token_embedding / text_projection keys)")
+        if self._text is None:
+            self._text = TextEncoder.from_state_dict(self._sd, self.device, max_batch=min(self._max_batch, 64))
+        return self._text.encode(text, normalise=False, out_dtype=self.dtype)
 
     def __call__(self, image, text=None):
         if text is not None:
@@ -190,6 +236,7 @@ def load(name, device="cuda", jit=False, download_root=None, state_dict=None, ra
                 f"{os.path.join(download_root or '~/.cache/clip', name.replace('/', '-') + '.pt')} "
                 "(or pass state_dict=..., or random_init=<seed> for benchmarking)")
         state_dict = random_visual_state_dict(name, int(seed))
+        state_dict.update(random_text_state_dict(name, int(seed)))
     else:
         state_dict = _unwrap(state_dict)
     missing = [k for k in weight_keys(GEOMETRY[name]["layers"], "visual.") if k not in state_dict]
@@ -199,6 +246,7 @@ def load(name, device="cuda", jit=False, download_root=None, state_dict=None, ra
     return model, _transform(GEOMETRY[name]["image_size"])
 
 
-def tokenize(texts, context_length=77, truncate=False):
-    raise NotImplementedError("clip.tokenize needs the BPE vocabulary of openai/CLIP, which is absent on this box; "
-                              "the text tower is SURVEY.md 8(f) row 1 (next)")
+def tokenize(texts, context_length=77, truncate=False, bpe_path=None):
+    """clip.tokenize(list[str]) -> LongTensor[B, 77] (tokenizer.py: openai's byte-level BPE restated)."""
+    from .tokenizer import tokenize as _tokenize
+    return _tokenize(texts, context_length, truncate, bpe_path)

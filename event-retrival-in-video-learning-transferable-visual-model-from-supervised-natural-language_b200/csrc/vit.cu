@@ -183,7 +183,7 @@ static int encode_chunk(evr_vit* h, const void* pixels, int pix_dtype, int B, vo
   for (const LayerW& l : h->layers) {
     if (launch_layernorm(h->x, d, h->hbuf, d, 1, l.ln1_g, l.ln1_b, M, d, s)) return 1;
     if (gemm(h->hbuf, d, l.w_in, d, M, 3 * d, l.b_in, h->qkv, 3 * d, EPI_BF16, s)) return 1;
-    if (launch_attention(h->qkv, h->attn, B, L, d, h->cfg.heads, s)) return 1;
+    if (launch_attention(h->qkv, h->attn, B, L, d, h->cfg.heads, 0, s)) return 1;
     if (gemm(h->attn, d, l.w_out, d, M, d, l.b_out, h->x, d, EPI_F32_RESID, s)) return 1;
     if (launch_layernorm(h->x, d, h->hbuf, d, 1, l.ln2_g, l.ln2_b, M, d, s)) return 1;
     if (gemm(h->hbuf, d, l.w_fc, d, M, 4 * d, l.b_fc, h->fbuf, 4 * d, EPI_BF16_GELU, s)) return 1;

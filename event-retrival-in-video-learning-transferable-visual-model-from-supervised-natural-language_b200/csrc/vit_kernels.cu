@@ -1,6 +1,8 @@
 // Non-GEMM kernels of the CLIP vision tower: im2col(+normalise), cls rows, LayerNorm, attention core,
 // final L2-normalise/cast and the one-off weight repacking.  Structure follows openai/CLIP
 // clip/model.py VisionTransformer.forward / ResidualAttentionBlock.
+#include <climits>
+
 #include "vit_kernels.cuh"
 
 #include <cmath>
@@ -125,10 +127,13 @@ layernorm_kernel(const float* in, size_t in_stride, void* out, size_t out_stride
 
 int launch_layernorm(const float* in, size_t in_stride, void* out, size_t out_stride, int out_bf16,
                      const float* gamma, const float* beta, int rows, int d, cudaStream_t stream) {
-  EVR_REQUIRE(d == 768 || d == 1024, "layernorm: width %d unsupported (768 | 1024)", d);
+  EVR_REQUIRE(d == 512 || d == 768 || d == 1024, "layernorm: width %d unsupported (512 | 768 | 1024)", d);
   const int blocks = (rows + 7) / 8;
   ProfScope ps(PF_LN, stream);
-  if (d == 768) {
+  if (d == 512) {
+    if (out_bf16) EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<4, true>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows));
+    else EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<4, false>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows));
+  } else if (d == 768) {
     if (out_bf16) EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<6, true>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows));
     else EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<6, false>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows));
   } else {
@@ -158,7 +163,8 @@ __device__ __forceinline__ uint32_t pack2_bf16(float lo, float hi) {
 constexpr int kAttnKStride = 72;  // bf16 elements per K row in smem (64 + 8 pad: conflict-free fragments)
 
 __global__ void __launch_bounds__(128)
-attention_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, int L, int d, float scale) {
+attention_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, int L, int d, float scale,
+                 int causal) {
   pdl_launch_dependents();
   pdl_wait();
   extern __shared__ __align__(16) uint8_t attn_smem[];
@@ -221,10 +227,13 @@ attention_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restric
 #pragma unroll
       for (int nt = 0; nt < 8; ++nt) {
         const int col = kb * 64 + nt * 8 + 2 * t;
-        s[nt][0] = col < L ? s[nt][0] * scale : -INFINITY;
-        s[nt][1] = col + 1 < L ? s[nt][1] * scale : -INFINITY;
-        s[nt][2] = col < L ? s[nt][2] * scale : -INFINITY;
-        s[nt][3] = col + 1 < L ? s[nt][3] * scale : -INFINITY;
+        // key limit of a query row: all L keys (vision tower), keys <= row under the text tower's causal mask
+        // (clip/model.py build_attention_mask: -inf above the diagonal)
+        const int lim0 = causal ? min(L, r0 + 1) : L, lim1 = causal ? min(L, r1 + 1) : L;
+        s[nt][0] = col < lim0 ? s[nt][0] * scale : -INFINITY;
+        s[nt][1] = col + 1 < lim0 ? s[nt][1] * scale : -INFINITY;
+        s[nt][2] = col < lim1 ? s[nt][2] * scale : -INFINITY;
+        s[nt][3] = col + 1 < lim1 ? s[nt][3] * scale : -INFINITY;
         mx0 = fmaxf(mx0, fmaxf(s[nt][0], s[nt][1]));
         mx1 = fmaxf(mx1, fmaxf(s[nt][2], s[nt][3]));
       }
@@ -232,7 +241,7 @@ attention_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restric
       mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
       mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
       mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
-      const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);  // finite: every key block holds >= 1 valid key
+      const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);  // finite: key block 0 always holds a valid key (col 0)
       const float a0 = __expf(m0 - mn0), a1 = __expf(m1 - mn1);
       l0 *= a0; l1 *= a1;
 #pragma unroll
@@ -444,10 +453,10 @@ attention_short_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __r
   }
 }
 
-int launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int d, int heads,
+int launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int d, int heads, int causal,
                      cudaStream_t stream) {
   EVR_REQUIRE(heads * 64 == d, "attention: head dim must be 64 (d=%d heads=%d)", d, heads);
-  if (L <= 64) {
+  if (L <= 64 && !causal) {
     static bool configured_short = false;
     if (!configured_short) {
       EVR_CHECK_CUDA(cudaFuncSetAttribute(attention_short_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -472,7 +481,71 @@ int launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L,
     configured = smem;
   }
   ProfScope ps(PF_ATTN, stream);
-  EVR_CHECK_CUDA(launch_pdl(attention_kernel, dim3(dim3(heads, B)), dim3(128), smem, stream, qkv, out, L, d, 0.125f));
+  EVR_CHECK_CUDA(launch_pdl(attention_kernel, dim3(dim3(heads, B)), dim3(128), smem, stream, qkv, out, L, d, 0.125f, causal));
+  EVR_CHECK_LAUNCH();
+  return 0;
+}
+
+// ----------------------------------------------------------------------------- text tower helpers
+// x[b*L + l, :] = token_embedding[tokens[b, l], :] + positional_embedding[l, :]   (clip/model.py CLIP.encode_text)
+__global__ void __launch_bounds__(128)
+embed_tokens_kernel(const int32_t* __restrict__ tokens, const float* __restrict__ table, const float* __restrict__ pos,
+                    float* __restrict__ x, int rows, int L, int d, int vocab) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int row = blockIdx.x;
+  if (row >= rows) return;
+  int tok = tokens[row];
+  tok = tok < 0 ? 0 : (tok >= vocab ? vocab - 1 : tok);  // ids are validated on the host; never read out of bounds
+  const float4* e = reinterpret_cast<const float4*>(table + static_cast<size_t>(tok) * d);
+  const float4* p = reinterpret_cast<const float4*>(pos + static_cast<size_t>(row % L) * d);
+  float4* o = reinterpret_cast<float4*>(x + static_cast<size_t>(row) * d);
+  for (int i = threadIdx.x; i < d / 4; i += blockDim.x) {
+    const float4 a = __ldg(e + i), b = __ldg(p + i);
+    o[i] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+  }
+}
+
+int launch_embed_tokens(const int32_t* tokens, const float* table, const float* pos, float* x, int B, int L, int d,
+                        int vocab, cudaStream_t stream) {
+  ProfScope ps(PF_VIT_MISC, stream);
+  EVR_CHECK_CUDA(launch_pdl(embed_tokens_kernel, dim3(B * L), dim3(128), 0, stream, tokens, table, pos, x, B * L, L, d,
+                            vocab));
+  EVR_CHECK_LAUNCH();
+  return 0;
+}
+
+// out[b, :] = x[b*L + argmax_l tokens[b, l], :]  -- the EOT token carries the largest id (encode_text:
+// x[arange(B), text.argmax(dim=-1)]); first occurrence on ties, as torch.argmax.
+__global__ void __launch_bounds__(128)
+gather_eot_kernel(const int32_t* __restrict__ tokens, const float* __restrict__ x, float* __restrict__ out, int L,
+                  int d) {
+  pdl_launch_dependents();
+  pdl_wait();
+  __shared__ int best_pos;
+  const int b = blockIdx.x;
+  if (threadIdx.x < 32) {
+    int bv = INT_MIN, bp = 0;
+    for (int l = threadIdx.x; l < L; l += 32) {
+      const int v = tokens[b * L + l];
+      if (v > bv) { bv = v; bp = l; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const int ov = __shfl_xor_sync(0xffffffffu, bv, o), op = __shfl_xor_sync(0xffffffffu, bp, o);
+      if (ov > bv || (ov == bv && op < bp)) { bv = ov; bp = op; }
+    }
+    if (threadIdx.x == 0) best_pos = bp;
+  }
+  __syncthreads();
+  const float4* src = reinterpret_cast<const float4*>(x + (static_cast<size_t>(b) * L + best_pos) * d);
+  float4* dst = reinterpret_cast<float4*>(out + static_cast<size_t>(b) * d);
+  for (int i = threadIdx.x; i < d / 4; i += blockDim.x) dst[i] = src[i];
+}
+
+int launch_gather_eot(const int32_t* tokens, const float* x, float* out, int B, int L, int d, cudaStream_t stream) {
+  ProfScope ps(PF_VIT_MISC, stream);
+  EVR_CHECK_CUDA(launch_pdl(gather_eot_kernel, dim3(B), dim3(128), 0, stream, tokens, x, out, L, d));
   EVR_CHECK_LAUNCH();
   return 0;
 }

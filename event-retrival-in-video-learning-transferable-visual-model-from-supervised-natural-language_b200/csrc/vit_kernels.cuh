@@ -20,9 +20,14 @@ int launch_cls_rows(float* x, const float* cls, const float* pos, int B, int L, 
 int launch_layernorm(const float* in, size_t in_stride, void* out, size_t out_stride, int out_bf16,
                      const float* gamma, const float* beta, int rows, int d, cudaStream_t stream);
 
-// softmax(q k^T / sqrt(hd)) v per (image, head); qkv bf16 [B*L, 3d] (q | k | v), out bf16 [B*L, d]. hd = 64.
-int launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int d, int heads,
+// softmax(q k^T / sqrt(hd) [+ causal mask]) v per (sequence, head); qkv bf16 [B*L, 3d] (q | k | v), out bf16 [B*L, d]. hd = 64.
+int launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int d, int heads, int causal,
                      cudaStream_t stream);
+
+// text tower: x = token_embedding[tokens] + positional_embedding ; EOT-row gather (argmax of the token ids)
+int launch_embed_tokens(const int32_t* tokens, const float* table, const float* pos, float* x, int B, int L, int d,
+                        int vocab, cudaStream_t stream);
+int launch_gather_eot(const int32_t* tokens, const float* x, float* out, int B, int L, int d, cudaStream_t stream);
 
 // out[r] = in[r] (/ ||in[r]||) ; out fp32 (out_dtype 0) or fp16 (1)
 int launch_l2norm_cast(const float* in, void* out, int out_dtype, int rows, int D, int normalise,

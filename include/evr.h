@@ -93,6 +93,32 @@ int evr_vit_destroy(evr_vit* h);
 int evr_vit_encode(evr_vit* h, const void* pixels, int pix_dtype, int B, void* out, int out_dtype,
                    int l2_normalise, void* stream);
 
+/* ---- CLIP text tower (encode_text) ---------------------------------------------------
+ * replaces  model.encode_text(clip.tokenize([query]))   Backend/services/embedding_service.py:169-177
+ *           (openai/CLIP CLIP.encode_text: causal transformer, EOT row, @ text_projection)
+ * Weight order (fp32 device pointers, openai state_dict keys of the whole CLIP):
+ *   0 token_embedding.weight [vocab,d]   1 positional_embedding [ctx,d]
+ *   per layer i, base 2 + 12*i: transformer.resblocks.i.{ln_1.weight, ln_1.bias, attn.in_proj_weight [3d,d],
+ *     attn.in_proj_bias, attn.out_proj.weight, attn.out_proj.bias, ln_2.weight, ln_2.bias, mlp.c_fc.weight [4d,d],
+ *     mlp.c_fc.bias, mlp.c_proj.weight [d,4d], mlp.c_proj.bias}
+ *   then ln_final.weight, ln_final.bias, text_projection [d,out]
+ * tokens: [B, context_length] int32 device ids as clip.tokenize emits them (the EOT id is the largest of a row).
+ * out: [B, out_dim] fp32 (out_dtype 0) or fp16 (1); l2_normalise != 0 applies x / ||x|| (embedding_service.py:180). */
+typedef struct evr_text evr_text;
+typedef struct {
+  int context_length; /* 77 */
+  int vocab_size;     /* 49408 */
+  int width;          /* 512 | 768 */
+  int layers;         /* 12 */
+  int heads;          /* width / 64 */
+  int out_dim;        /* 512 | 768 */
+} evr_text_cfg;
+int evr_text_create(const evr_text_cfg* cfg, const void* const* weights_fp32, int n_weights, int max_batch,
+                    evr_text** out);
+int evr_text_destroy(evr_text* h);
+int evr_text_encode(evr_text* h, const int32_t* tokens, int B, void* out, int out_dtype, int l2_normalise,
+                    void* stream);
+
 /* building-block GEMM exported for the parity tests:  C[M,N] = A[M,K] * W[N,K]^T (+bias)
  * A, W bf16 row-major; epilogue 0: bf16 out (+bias), 1: bias+QuickGELU bf16,
  * 2: fp32 out = acc + bias + residual (in place on out). */
