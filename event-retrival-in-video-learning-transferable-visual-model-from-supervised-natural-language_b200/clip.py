@@ -212,9 +212,11 @@ class CLIPModel:
 def _transform(n_px):
     """clip/clip.py `_transform`: Resize(bicubic) -> CenterCrop -> RGB -> ToTensor -> Normalize (host side, PIL)."""
     from torchvision import transforms as T
-    return T.Compose([
+    t = T.Compose([
         T.Resize(n_px, interpolation=T.InterpolationMode.BICUBIC), T.CenterCrop(n_px),
         lambda im: im.convert("RGB"), T.ToTensor(), T.Normalize(CLIP_MEAN, CLIP_STD)])
+    t.evr_n_px = n_px  # lets the ingest loop swap in the bit-identical device path (preprocess.GpuPreprocess)
+    return t
 
 
 def load(name, device="cuda", jit=False, download_root=None, state_dict=None, random_init=None, max_batch=256):

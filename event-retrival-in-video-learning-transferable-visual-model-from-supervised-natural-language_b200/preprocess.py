@@ -1,0 +1,139 @@
+"""GPU image preprocessing: clip._transform's `Resize(n_px, BICUBIC)` + `CenterCrop(n_px)` on the device.
+
+Replaces the per-frame PIL work of `self.preprocess(Image.open(p).convert('RGB'))`
+(Backend/services/embedding_service.py:475, Backend/embedding.py:46).  The arithmetic is PIL's
+8-bit `ImagingResample` (libImaging/Resample.c): separable convolution, horizontal pass then vertical pass, cubic
+filter a = -0.5 with the support stretched by the down-scale factor (antialiasing), coefficients in 22-bit fixed point,
+intermediate image in uint8.  The coefficient tables are built here on the host in float64 exactly as the C code does;
+the two passes run as CUDA kernels in integers (csrc/preprocess.cu), so the result is bit-identical to PIL's
+(tests/test_preprocess.py checks the tables + integer arithmetic against PIL itself on CPU,
+tests/test_preprocess_gpu.py the kernels against PIL).  The output is uint8 [S, S, 3], which `VisionEncoder.encode` takes directly (ToTensor + Normalize fused).
+"""
+import ctypes
+import functools
+
+import numpy as np
+import torch
+
+from ._lib import lib, check, ptr, current_stream_ptr
+
+PRECISION_BITS = 32 - 8 - 2  # Resample.c
+
+
+def _bicubic(x):
+    a = -0.5
+    x = np.abs(x)
+    return np.where(x < 1.0, ((a + 2.0) * x - (a + 3.0)) * x * x + 1.0,
+                    np.where(x < 2.0, (((x - 5.0) * x + 8.0) * x - 4.0) * a, 0.0))
+
+
+@functools.lru_cache(maxsize=256)
+def resample_coeffs(in_size, out_size):
+    """precompute_coeffs + normalize_coeffs_8bpc of Resample.c for the BICUBIC filter (support 2.0) over the full
+    input range [0, in_size).  -> (bounds int32 [out, 2] = (xmin, count), kk int32 [out, ksize])."""
+    support0 = 2.0
+    scale = filterscale = float(in_size) / out_size
+    if filterscale < 1.0:
+        filterscale = 1.0
+    support = support0 * filterscale
+    ksize = int(np.ceil(support)) * 2 + 1
+    bounds = np.zeros((out_size, 2), dtype=np.int32)
+    kk = np.zeros((out_size, ksize), dtype=np.int32)
+    ss = 1.0 / filterscale
+    for xx in range(out_size):
+        center = (xx + 0.5) * scale
+        xmin = int(center - support + 0.5)
+        if xmin < 0:
+            xmin = 0
+        xmax = int(center + support + 0.5)
+        if xmax > in_size:
+            xmax = in_size
+        xmax -= xmin
+        k = _bicubic((np.arange(xmax, dtype=np.float64) + xmin - center + 0.5) * ss)
+        ww = 0.0
+        for v in k:            # sequential double accumulation, as the C loop
+            ww += v
+        if ww != 0.0:
+            k = k / ww
+        fixed = np.where(k < 0, -0.5 + k * (1 << PRECISION_BITS), 0.5 + k * (1 << PRECISION_BITS))
+        kk[xx, :xmax] = np.trunc(fixed).astype(np.int32)   # C (int) cast truncates toward zero
+        bounds[xx] = (xmin, xmax)
+    return bounds, kk
+
+
+def resized_size(w, h, n_px):
+    """torchvision Resize(int): the smaller edge becomes n_px, the other int(n_px * long / short)."""
+    if w <= h:
+        return n_px, int(n_px * h / w)
+    return int(n_px * w / h), n_px
+
+
+def crop_origin(w, h, n_px):
+    """torchvision CenterCrop: (left, top) = round((size - n_px) / 2)."""
+    return int(round((w - n_px) / 2.0)), int(round((h - n_px) / 2.0))
+
+
+def plan(w, h, n_px):
+    """Everything the two device passes need for a w x h source: tables restricted to the cropped window."""
+    rw, rh = resized_size(w, h, n_px)
+    left, top = crop_origin(rw, rh, n_px)
+    hb, hk = resample_coeffs(w, rw)
+    vb, vk = resample_coeffs(h, rh)
+    hb, hk = hb[left:left + n_px], hk[left:left + n_px]
+    vb, vk = vb[top:top + n_px], vk[top:top + n_px]
+    y0 = int(vb[:, 0].min())
+    y1 = int((vb[:, 0] + vb[:, 1]).max())
+    return dict(rw=rw, rh=rh, left=left, top=top, hb=np.ascontiguousarray(hb), hk=np.ascontiguousarray(hk),
+                vb=np.ascontiguousarray(vb), vk=np.ascontiguousarray(vk), y0=y0, rows=y1 - y0)
+
+
+class GpuPreprocess:
+    """Resize(n_px, BICUBIC) + CenterCrop(n_px) for batches of decoded frames of one size.
+
+    __call__(frames): uint8 [B, H, W, 3] (numpy or torch, host or device; a single [H, W, 3] frame or a PIL image is
+    accepted too) -> uint8 device tensor [B, n_px, n_px, 3], bit-identical to the PIL pipeline.  Feed it to
+    `VisionEncoder.encode` / `model.encode_image`, which fuse ToTensor + Normalize."""
+
+    def __init__(self, n_px=224, device="cuda"):
+        self.n_px = int(n_px)
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("GpuPreprocess runs on a CUDA device only (the host path is clip.load's preprocess)")
+        self._plans = {}
+
+    def _plan(self, w, h):
+        key = (w, h)
+        if key not in self._plans:
+            p = plan(w, h, self.n_px)
+            dev = {k: torch.from_numpy(p[k]).to(self.device) for k in ("hb", "hk", "vb", "vk")}
+            self._plans[key] = (p, dev)
+        return self._plans[key]
+
+    @torch.no_grad()
+    def __call__(self, frames):
+        if hasattr(frames, "convert"):  # PIL image
+            frames = np.array(frames.convert("RGB"))
+        if isinstance(frames, np.ndarray):
+            frames = torch.from_numpy(np.ascontiguousarray(frames))
+        if frames.dim() == 3:
+            frames = frames.unsqueeze(0)
+        if frames.dtype != torch.uint8 or frames.dim() != 4 or frames.shape[-1] != 3:
+            raise ValueError(f"frames must be uint8 [B, H, W, 3], got {frames.dtype} {tuple(frames.shape)}")
+        src = frames.to(self.device).contiguous()
+        B, H, W, _ = src.shape
+        S = self.n_px
+        out = torch.empty((B, S, S, 3), dtype=torch.uint8, device=self.device)
+        if B == 0:
+            return out
+        p, dev = self._plan(W, H)
+        done = 0
+        with torch.cuda.device(self.device):
+            while done < B:  # grid.z limit
+                nb = min(B - done, 32768)
+                tmp = torch.empty((nb, p["rows"], S, 3), dtype=torch.uint8, device=self.device)
+                check(lib.evr_resize_crop_u8(ptr(src[done:done + nb]), nb, H, W, S, ptr(dev["hb"]), ptr(dev["hk"]),
+                                             dev["hk"].shape[1], ptr(dev["vb"]), ptr(dev["vk"]), dev["vk"].shape[1],
+                                             p["y0"], p["rows"], ptr(tmp), ptr(out[done:done + nb]),
+                                             current_stream_ptr()), "evr_resize_crop_u8")
+                done += nb
+        return out

@@ -20,6 +20,7 @@ import numpy as np
 import torch
 
 from . import clip as _clip
+from .preprocess import GpuPreprocess
 from .search import FrameStore
 
 IMAGE_EXT = ('.jpg', '.jpeg', '.png')  # embedding_service.py:452
@@ -152,16 +153,19 @@ class EmbeddingService:
     Extra keyword arguments (all optional, absent in the reference): `clip_module` (defaults to this package's
     `clip`), `model_name`, `load_kwargs` (forwarded to clip.load, e.g. state_dict= / random_init=),
     `text_encoder` (callable str -> [1, D] array, used while the text tower is not built: SURVEY 8f row 1),
-    `checkpoint_path` (fine-tuned CLIPWithClassifier checkpoint, embedding_service.py:93)."""
+    `checkpoint_path` (fine-tuned CLIPWithClassifier checkpoint, embedding_service.py:93), `gpu_preprocess` (ingest
+    resizes/crops on the device, bit-identical to PIL; False keeps the per-frame host `preprocess`)."""
 
     def __init__(self, cache_service, path_service, data_service, device="cuda", clip_module=None,
-                 model_name="ViT-B/32", load_kwargs=None, text_encoder=None, checkpoint_path=None):
+                 model_name="ViT-B/32", load_kwargs=None, text_encoder=None, checkpoint_path=None,
+                 gpu_preprocess=True):
         self.cache_service, self.path_service, self.data_service = cache_service, path_service, data_service
         self.device = device
         self._clip = clip_module or _clip
         self._model_name = model_name
         self._load_kwargs = dict(load_kwargs or {})
         self.text_encoder = text_encoder
+        self.gpu_preprocess = bool(gpu_preprocess)
         self.original_model, self.preprocess = self._clip.load(model_name, device=device, **self._load_kwargs)
         self.finetuned_model = None
         self.active_model = "original"
@@ -376,18 +380,44 @@ class EmbeddingService:
             print(f"No image files found in {folder_path}")
             return None
         S = self.original_model.visual.input_resolution
-        batch_size = 32  # :461
         all_embeddings, bad_rows = [], []
-        for i in range(0, len(frame_files), batch_size):
-            batch = []
-            for j, name in enumerate(frame_files[i:i + batch_size]):
+        if getattr(self.preprocess, "evr_n_px", None) == S and self.gpu_preprocess:
+            # device path: PIL only decodes; Resize(bicubic) + CenterCrop run on the GPU bit-identically to PIL
+            # (preprocess.py) and ToTensor + Normalize are fused into the encoder's im2col.  Frames of one size are
+            # batched together; the row order stays the sorted file order.
+            pre = self._gpu_pre = getattr(self, "_gpu_pre", None) or GpuPreprocess(S, self.device)
+            pending, shape = [], None
+
+            def flush():
+                if pending:
+                    u8 = pre(np.stack(pending))
+                    all_embeddings.append(self._encode_images(u8, key))
+                    pending.clear()
+
+            for i, name in enumerate(frame_files):
                 try:
-                    batch.append(self.preprocess(Image.open(os.path.join(folder_path, name)).convert('RGB')))
+                    frame = np.array(Image.open(os.path.join(folder_path, name)).convert('RGB'))
                 except Exception as e:
                     print(f"Error preprocessing image {name}: {e}")
-                    batch.append(torch.zeros(3, S, S))
-                    bad_rows.append(i + j)
-            all_embeddings.append(self._encode_images(torch.stack(batch).to(self.device), key))
+                    frame = np.zeros(shape or (S, S, 3), dtype=np.uint8)
+                    bad_rows.append(i)
+                if frame.shape != shape or len(pending) == 256:
+                    flush()
+                    shape = frame.shape
+                pending.append(frame)
+            flush()
+        else:
+            batch_size = 32  # :461
+            for i in range(0, len(frame_files), batch_size):
+                batch = []
+                for j, name in enumerate(frame_files[i:i + batch_size]):
+                    try:
+                        batch.append(self.preprocess(Image.open(os.path.join(folder_path, name)).convert('RGB')))
+                    except Exception as e:
+                        print(f"Error preprocessing image {name}: {e}")
+                        batch.append(torch.zeros(3, S, S))
+                        bad_rows.append(i + j)
+                all_embeddings.append(self._encode_images(torch.stack(batch).to(self.device), key))
         embeddings = np.vstack(all_embeddings)
         norm = np.linalg.norm(embeddings, axis=-1, keepdims=True)
         embeddings = embeddings / np.where(norm > 1e-8, norm, 1).astype(embeddings.dtype)
@@ -424,7 +454,8 @@ class _FinetunedImageEncoder:
         self.clip_model = clip_model.float()
 
     def __call__(self, images, texts=None, get_embeddings=False):
-        f = self.clip_model.encode_image(images.float()).float()
+        # uint8 [B,S,S,3] frames (device preprocessing path) go straight in: ToTensor + Normalize are fused in the tower
+        f = self.clip_model.encode_image(images if images.dtype == torch.uint8 else images.float()).float()
         return f / f.norm(dim=-1, keepdim=True)
 
     def eval(self):

@@ -93,6 +93,18 @@ int evr_vit_destroy(evr_vit* h);
 int evr_vit_encode(evr_vit* h, const void* pixels, int pix_dtype, int B, void* out, int out_dtype,
                    int l2_normalise, void* stream);
 
+/* ---- frame preprocessing ---------------------------------------------------------------
+ * replaces  Resize(n_px, BICUBIC) + CenterCrop(n_px) of clip._transform (PIL ImagingResample, 8 bits per channel)
+ *           inside self.preprocess(Image.open(p).convert('RGB'))   Backend/services/embedding_service.py:475
+ * src [B, H, W, 3] uint8 RGB (decoded frames of one size) -> dst [B, S, S, 3] uint8, bit-identical to PIL.
+ * hbounds [S, 2] (xmin, taps) and hk [S, hksize]: horizontal coefficients of the S cropped output columns in PIL's
+ * 22-bit fixed point; vbounds / vk likewise for the S cropped output rows (ymin in source rows).  Source rows
+ * [y0, y0 + rows) are the ones the vertical pass reads; tmp [B, rows, S, 3] uint8 is the intermediate image.
+ * preprocess.py builds the tables (float64, as Resample.c precompute_coeffs / normalize_coeffs_8bpc). */
+int evr_resize_crop_u8(const uint8_t* src, int B, int H, int W, int S, const int32_t* hbounds, const int32_t* hk,
+                       int hksize, const int32_t* vbounds, const int32_t* vk, int vksize, int y0, int rows,
+                       uint8_t* tmp, uint8_t* dst, void* stream);
+
 /* ---- CLIP text tower (encode_text) ---------------------------------------------------
  * replaces  model.encode_text(clip.tokenize([query]))   Backend/services/embedding_service.py:169-177
  *           (openai/CLIP CLIP.encode_text: causal transformer, EOT row, @ text_projection)

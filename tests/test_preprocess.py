@@ -1,0 +1,34 @@
+"""Preprocessing tables + integer arithmetic against PIL itself (CPU): clip._transform's Resize(224, BICUBIC) +
+CenterCrop(224) must be reproduced bit for bit (the CUDA kernels perform exactly `resample_reference_u8`)."""
+import importlib
+
+import numpy as np
+import pytest
+
+from conftest import PKG
+from oracle import preprocess_oracle as po
+
+SIZES = [(360, 640), (720, 1280), (224, 224), (300, 224), (500, 333), (100, 160), (1080, 1920), (225, 400), (37, 911)]
+
+
+@pytest.mark.parametrize("h,w", SIZES)
+def test_tables_and_integer_passes_equal_pil(h, w):
+    pp = importlib.import_module(PKG + ".preprocess")
+    rng = np.random.default_rng(h * 10007 + w)
+    img = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+    img[: h // 3] = np.where(rng.random((h // 3, w, 1)) < 0.5, 0, 255)   # hard edges: the cubic lobes overshoot -> clip8
+    ref = po.pil_transform_u8(img, 224)
+    out = po.resample_reference_u8(img, pp.plan(w, h, 224), 224)
+    assert np.array_equal(ref, out)
+
+
+def test_geometry_rules():
+    pp = importlib.import_module(PKG + ".preprocess")
+    assert pp.resized_size(640, 360, 224) == (398, 224) and pp.resized_size(360, 640, 224) == (224, 398)
+    assert pp.resized_size(333, 500, 224) == (224, 336)
+    assert pp.crop_origin(398, 224, 224) == (87, 0) and pp.crop_origin(224, 337, 224) == (0, 56)  # round half to even
+    b, k = pp.resample_coeffs(448, 224)
+    assert k.shape == (224, 9) and (k.sum(1) - (1 << 22)).__abs__().max() <= 8   # rows sum to 1.0 in 22-bit fixed point
+    assert (b[:, 0] >= 0).all() and (b[:, 0] + b[:, 1] <= 448).all()
+    b, k = pp.resample_coeffs(224, 224)
+    assert ((k != 0).sum(1) == 1).all() and (k.max(1) == 1 << 22).all()         # identity scale: one unit tap per row

@@ -88,6 +88,11 @@ def test_ingest_writes_reference_layout(tmp_path, cuda, visual, full_sd):
     meta = json.load(open(ps.get_metadata_path("vid")))
     assert all(item["embedding_model"] == "original" for item in meta)
     assert svc.get_active_model_name() == "original"
+    # the device resize/crop path (default) and the per-frame host `preprocess` path see identical pixels
+    assert svc.gpu_preprocess
+    svc.gpu_preprocess = False
+    host = np.load(svc.extract_and_save_embeddings_from_folder(folder, None, "vid"))
+    assert np.abs(host.astype(np.float32) - out.astype(np.float32)).max() <= 2e-3
 
 
 def test_ingest_edge_cases(tmp_path, cuda, full_sd):
