@@ -1,5 +1,7 @@
 // Host side of the tcgen05 GEMM: tile-shape choice, tensor maps, launch; plus the exported
 // building-block entry point evr_gemm_bf16 (include/evr.h) used by the parity tests.
+#include <cstdlib>
+
 #include "gemm_tc.cuh"
 
 #include "../../include/evr.h"
@@ -59,10 +61,10 @@ static int choose_block_n(int M, int N, int units, int tile_m) {
   for (int bn : cands) {
     const int tiles = num_m * ((N + bn - 1) / bn);
     const int rounds = (tiles + units - 1) / units;
-    // time per tile and k-block: the larger of the MMA time (~ tile_m * bn) and the operand delivery time (~ tile_m + bn
-    // rows of 128 B through L2 -> SM at the measured ~9.5 TB/s: 1.45 clk per row against 2 clk per 256 x 1 of MMA)
-    const double mma = 2.0 * bn * tile_m / 256.0, feed = 1.45 * (tile_m + bn);
-    double cost = static_cast<double>(rounds) * (mma > feed ? mma : feed);
+    // time per tile ~ BLOCK_N (rounds of the persistent grid dominate); 128-wide tiles move more operand bytes per
+    // FLOP.  Measured on M=12800 (ncu, warm): N=3072 -> 55.1 / 50.9 / 52.2 us for BLOCK_N 128 / 192 / 256,
+    // N=2304 -> 43.3 / 41.3 / 41.9, N=768,K=3072 -> 51.0 / 46.1 / 56.7: the round count decides.
+    double cost = static_cast<double>(rounds) * bn * (bn == 128 ? 1.06 : 1.0);
     if (cost < best_cost) { best_cost = cost; best = bn; }
   }
   return best;
@@ -78,7 +80,11 @@ int launch_gemm_bf16(const void* A, int lda, const void* W, int ldw, const GemmA
   // CTA pairs (256-row tiles) whenever there is more than one 128-row tile of work
   const int cg = (args.M > kGemmBlockM && sms % 2 == 0) ? 2 : 1;
   const int units = sms / cg, tile_m = kGemmBlockM * cg;
-  const int bn = choose_block_n(args.M, args.N, units, tile_m);
+  int bn = choose_block_n(args.M, args.N, units, tile_m);
+  if (const char* e = getenv("EVR_GEMM_BN")) {  // developer override for tile-shape experiments
+    const int v = atoi(e);
+    if (v == 128 || v == 192 || v == 256) bn = v;
+  }
   CUtensorMap ta, tb;
   if (int r = make_tmap_2d_16b(&ta, A, args.M, args.K, static_cast<uint64_t>(lda) * 2, kGemmBlockM, true)) return r;
   if (int r = make_tmap_2d_16b(&tb, W, args.N, args.K, static_cast<uint64_t>(ldw) * 2, bn / cg, true)) return r;

@@ -324,6 +324,12 @@ __device__ __forceinline__ void ldmatrix_x4_trans(uint32_t (&r)[4], const void* 
                : "r"(static_cast<uint32_t>(__cvta_generic_to_shared(smem_src))));
 }
 
+__device__ __forceinline__ float fast_exp2(float x) {  // ex2.approx: 2 ulp, exp2(-inf) = 0
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 __global__ void __launch_bounds__(128)
 attention_short_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, int L, int d, int heads,
                        int items, float scale_log2e) {
@@ -342,10 +348,16 @@ attention_short_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __r
     const int b = item / heads, h = item - b * heads;
     const __nv_bfloat16* src = qkv + static_cast<size_t>(b) * L * ld + h * 64;
     uint8_t* dst = attn_smem + stage * kAttnStageBytes;
-    for (int i = threadIdx.x; i < 3 * L * 8; i += 128) {   // 16-B chunks: (tile, row, chunk)
-      const int tile = i / (L * 8), rem = i - tile * (L * 8), r = rem >> 3, c = rem & 7;
-      cp_async16(dst + tile * kAttnTileBytes + r * (kAttnKStride * 2) + c * 16,
-                 src + static_cast<size_t>(r) * ld + tile * d + c * 8);
+    // 16-B chunks: thread -> (row = tid / 8 + 16 j, chunk = tid % 8) of each of the three tiles; no index division
+    const int c = threadIdx.x & 7;
+    const __nv_bfloat16* s0 = src + c * 8;
+    uint8_t* d0 = dst + c * 16;
+    for (int r = threadIdx.x >> 3; r < L; r += 16) {
+      const __nv_bfloat16* sr = s0 + static_cast<size_t>(r) * ld;
+      uint8_t* dr = d0 + r * (kAttnKStride * 2);
+      cp_async16(dr, sr);
+      cp_async16(dr + kAttnTileBytes, sr + d);
+      cp_async16(dr + 2 * kAttnTileBytes, sr + 2 * d);
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
@@ -401,10 +413,10 @@ attention_short_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __r
       float l0 = 0.f, l1 = 0.f;
 #pragma unroll
       for (int nt = 0; nt < 8; ++nt) {
-        s[nt][0] = exp2f(s[nt][0] - mx0);
-        s[nt][1] = exp2f(s[nt][1] - mx0);
-        s[nt][2] = exp2f(s[nt][2] - mx1);
-        s[nt][3] = exp2f(s[nt][3] - mx1);
+        s[nt][0] = fast_exp2(s[nt][0] - mx0);
+        s[nt][1] = fast_exp2(s[nt][1] - mx0);
+        s[nt][2] = fast_exp2(s[nt][2] - mx1);
+        s[nt][3] = fast_exp2(s[nt][3] - mx1);
         l0 += s[nt][0] + s[nt][1];
         l1 += s[nt][2] + s[nt][3];
       }
