@@ -13,45 +13,82 @@ namespace evr {
 __constant__ float c_clip_mean[3] = {0.48145466f, 0.4578275f, 0.40821073f};
 __constant__ float c_clip_std[3] = {0.26862954f, 0.26130258f, 0.27577711f};
 
+// One warp per image line.  uint8 NHWC: the line (b, y) is S*3 contiguous bytes holding all three channels; fp32 NCHW:
+// the line (b, c, y) is S contiguous floats.  A line feeds g patches: for every (patch px, channel c) it contributes
+// the run out[row(b, py, px)][c*P*P + ky*P + 0..P-1].  Lanes walk the 3S (or S) outputs of the line two at a time, so
+// global reads are whole lines and writes are bf16x2 along contiguous runs.  ToTensor + Normalize
+// ((v/255 - mean)/std, clip._transform) come from a 3 x 256 table built per block with the same fp32 operations.
+template <int P, bool U8>
 __global__ void __launch_bounds__(256)
-im2col_kernel(const void* __restrict__ pixels, int pix_dtype, size_t total_pairs, int S, int p, int g, int K, int Kp,
-              __nv_bfloat16* __restrict__ out) {
+im2col_lines_kernel(const void* __restrict__ pixels, int lines, int S, int Kp, __nv_bfloat16* __restrict__ out) {
   pdl_launch_dependents();
   pdl_wait();
-  const size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (idx >= total_pairs) return;
-  const int half_k = K >> 1;
-  const int col = 2 * static_cast<int>(idx % half_k);
-  const size_t row = idx / half_k;
-  const int pp = p * p;
-  const int c = col / pp, rem = col - c * pp;
-  const int ky = rem / p, kx = rem - ky * p;
-  const int gg = g * g;
-  const int b = static_cast<int>(row / gg), pr = static_cast<int>(row - static_cast<size_t>(b) * gg);
-  const int py = pr / g, px = pr - py * g;
-  const int y = py * p + ky, x = px * p + kx;
-  float v0, v1;
-  if (pix_dtype == 0) {
-    const float* src = static_cast<const float*>(pixels) + ((static_cast<size_t>(b) * 3 + c) * S + y) * S + x;
-    const float2 t = *reinterpret_cast<const float2*>(src);
-    v0 = t.x; v1 = t.y;
-  } else {
-    const uint8_t* src = static_cast<const uint8_t*>(pixels) + ((static_cast<size_t>(b) * S + y) * S + x) * 3 + c;
-    const float m = c_clip_mean[c], s = c_clip_std[c];
-    v0 = (static_cast<float>(src[0]) / 255.0f - m) / s;
-    v1 = (static_cast<float>(src[3]) / 255.0f - m) / s;
+  __shared__ __nv_bfloat16 lut[3][256];
+  __shared__ __align__(16) uint8_t line_buf[8][U8 ? 3 * 224 + 32 : 16];
+  if constexpr (U8) {
+    for (int i = threadIdx.x; i < 768; i += 256) {
+      const int c = i >> 8, v = i & 255;
+      lut[c][v] = __float2bfloat16_rn((static_cast<float>(v) / 255.0f - c_clip_mean[c]) / c_clip_std[c]);
+    }
+    __syncthreads();
   }
-  *reinterpret_cast<__nv_bfloat162*>(out + row * Kp + col) = __floats2bfloat162_rn(v0, v1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int line = blockIdx.x * 8 + warp;
+  if (line >= lines) return;
+  const int g = S / P;
+  constexpr int PP = P * P;
+  if constexpr (U8) {
+    const int b = line / S, y = line - b * S;
+    const int py = y / P, ky = y - py * P;
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(static_cast<const uint8_t*>(pixels) +
+                                                            static_cast<size_t>(line) * S * 3);  // S*3 % 4 == 0
+    uint32_t* buf = reinterpret_cast<uint32_t*>(line_buf[warp]);
+    for (int i = lane; i < S * 3 / 4; i += 32) buf[i] = __ldg(src + i);
+    __syncwarp();
+    const uint8_t* lb = line_buf[warp];
+    __nv_bfloat16* obase = out + (static_cast<size_t>(b) * g * g + static_cast<size_t>(py) * g) * Kp + ky * P;
+    for (int e = 2 * lane; e < 3 * S; e += 64) {       // e = (px*3 + c)*P + kx, kx even
+      const int run = e / P, kx = e - run * P;
+      const int px = run / 3, c = run - px * 3;
+      const int x = px * P + kx;
+      const __nv_bfloat162 v = __halves2bfloat162(lut[c][lb[x * 3 + c]], lut[c][lb[x * 3 + 3 + c]]);
+      *reinterpret_cast<__nv_bfloat162*>(obase + static_cast<size_t>(px) * Kp + c * PP + kx) = v;
+    }
+  } else {
+    const int b = line / (3 * S), rem = line - b * 3 * S;
+    const int c = rem / S, y = rem - c * S;
+    const int py = y / P, ky = y - py * P;
+    const float2* src = reinterpret_cast<const float2*>(static_cast<const float*>(pixels) + static_cast<size_t>(line) * S);
+    __nv_bfloat16* obase = out + (static_cast<size_t>(b) * g * g + static_cast<size_t>(py) * g) * Kp + c * PP + ky * P;
+    for (int x = 2 * lane; x < S; x += 64) {
+      const float2 t = __ldg(src + (x >> 1));
+      const int px = x / P, kx = x - px * P;
+      *reinterpret_cast<__nv_bfloat162*>(obase + static_cast<size_t>(px) * Kp + kx) = __floats2bfloat162_rn(t.x, t.y);
+    }
+  }
+}
+
+template <int P>
+static int launch_im2col_p(const void* pixels, int pix_dtype, int B, int S, int Kp, __nv_bfloat16* out,
+                           cudaStream_t stream) {
+  const int lines = pix_dtype == 1 ? B * S : B * 3 * S;
+  const unsigned blocks = static_cast<unsigned>((lines + 7) / 8);
+  if (pix_dtype == 1)
+    EVR_CHECK_CUDA(launch_pdl(im2col_lines_kernel<P, true>, dim3(blocks), dim3(256), 0, stream, pixels, lines, S, Kp, out));
+  else
+    EVR_CHECK_CUDA(launch_pdl(im2col_lines_kernel<P, false>, dim3(blocks), dim3(256), 0, stream, pixels, lines, S, Kp, out));
+  return 0;
 }
 
 int launch_im2col(const void* pixels, int pix_dtype, int B, int S, int p, int Kp, __nv_bfloat16* out,
                   cudaStream_t stream) {
   EVR_REQUIRE(S % p == 0 && p % 2 == 0, "im2col: image %d / patch %d unsupported", S, p);
-  const int g = S / p, K = 3 * p * p;
-  const size_t total = static_cast<size_t>(B) * g * g * (K / 2);
-  const unsigned blocks = static_cast<unsigned>((total + 255) / 256);
+  EVR_REQUIRE(S == 224 && (p == 32 || p == 16 || p == 14), "im2col: geometry %d / %d not instantiated (224 / 32|16|14)", S, p);
   ProfScope ps(PF_VIT_MISC, stream);
-  EVR_CHECK_CUDA(launch_pdl(im2col_kernel, dim3(blocks), dim3(256), 0, stream, pixels, pix_dtype, total, S, p, g, K, Kp, out));
+  int r = p == 32 ? launch_im2col_p<32>(pixels, pix_dtype, B, S, Kp, out, stream)
+          : p == 16 ? launch_im2col_p<16>(pixels, pix_dtype, B, S, Kp, out, stream)
+                    : launch_im2col_p<14>(pixels, pix_dtype, B, S, Kp, out, stream);
+  if (r) return r;
   EVR_CHECK_LAUNCH();
   return 0;
 }
