@@ -197,144 +197,13 @@ __device__ __forceinline__ uint32_t pack2_bf16(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&t);
 }
 
-constexpr int kAttnKStride = 72;  // bf16 elements per K row in smem (64 + 8 pad: conflict-free fragments)
-
-__global__ void __launch_bounds__(128)
-attention_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, int L, int d, float scale,
-                 int causal) {
-  pdl_launch_dependents();
-  pdl_wait();
-  extern __shared__ __align__(16) uint8_t attn_smem[];
-  const int h = blockIdx.x, b = blockIdx.y;
-  const int Lp = (L + 63) & ~63;
-  __nv_bfloat16* Ks = reinterpret_cast<__nv_bfloat16*>(attn_smem);  // [Lp][72]
-  __nv_bfloat16* Vs = Ks + Lp * kAttnKStride;                       // [Lp][72]  (row-major; the P.V operand is read
-                                                                    //  with ldmatrix.trans, no transposed copy)
-  const size_t row0 = static_cast<size_t>(b) * L;
-  const int ld = 3 * d;
-
-  for (int i = threadIdx.x; i < Lp * 8; i += 128) {
-    const int r = i >> 3, c = i & 7;
-    uint4 kv = make_uint4(0, 0, 0, 0), vv = make_uint4(0, 0, 0, 0);
-    if (r < L) {
-      const __nv_bfloat16* base = qkv + (row0 + r) * ld + h * 64 + c * 8;
-      kv = *reinterpret_cast<const uint4*>(base + d);
-      vv = *reinterpret_cast<const uint4*>(base + 2 * d);
-    }
-    *reinterpret_cast<uint4*>(Ks + r * kAttnKStride + c * 8) = kv;
-    *reinterpret_cast<uint4*>(Vs + r * kAttnKStride + c * 8) = vv;
-  }
-  __syncthreads();
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
-  const int num_mt = (L + 15) >> 4;
-  for (int mt = warp; mt < num_mt; mt += 4) {
-    const int r0 = mt * 16 + g, r1 = r0 + 8;
-    uint32_t qa[4][4];
-    {
-      const __nv_bfloat16* q0 = qkv + (row0 + r0) * ld + h * 64;
-      const __nv_bfloat16* q1 = qkv + (row0 + r1) * ld + h * 64;
-#pragma unroll
-      for (int kk = 0; kk < 4; ++kk) {
-        qa[kk][0] = r0 < L ? *reinterpret_cast<const uint32_t*>(q0 + 16 * kk + 2 * t) : 0u;
-        qa[kk][1] = r1 < L ? *reinterpret_cast<const uint32_t*>(q1 + 16 * kk + 2 * t) : 0u;
-        qa[kk][2] = r0 < L ? *reinterpret_cast<const uint32_t*>(q0 + 16 * kk + 8 + 2 * t) : 0u;
-        qa[kk][3] = r1 < L ? *reinterpret_cast<const uint32_t*>(q1 + 16 * kk + 8 + 2 * t) : 0u;
-      }
-    }
-    float o[8][4];
-#pragma unroll
-    for (int nt = 0; nt < 8; ++nt) { o[nt][0] = o[nt][1] = o[nt][2] = o[nt][3] = 0.f; }
-    float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
-
-    for (int kb = 0; kb < Lp / 64; ++kb) {
-      float s[8][4];
-#pragma unroll
-      for (int nt = 0; nt < 8; ++nt) {
-        s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
-        const __nv_bfloat16* kr = Ks + (kb * 64 + nt * 8 + g) * kAttnKStride;
-#pragma unroll
-        for (int kk = 0; kk < 4; ++kk) {
-          const uint32_t b0 = *reinterpret_cast<const uint32_t*>(kr + 16 * kk + 2 * t);
-          const uint32_t b1 = *reinterpret_cast<const uint32_t*>(kr + 16 * kk + 8 + 2 * t);
-          mma_bf16_16816(s[nt], qa[kk], b0, b1);
-        }
-      }
-      float mx0 = -INFINITY, mx1 = -INFINITY;
-#pragma unroll
-      for (int nt = 0; nt < 8; ++nt) {
-        const int col = kb * 64 + nt * 8 + 2 * t;
-        // key limit of a query row: all L keys (vision tower), keys <= row under the text tower's causal mask
-        // (clip/model.py build_attention_mask: -inf above the diagonal)
-        const int lim0 = causal ? min(L, r0 + 1) : L, lim1 = causal ? min(L, r1 + 1) : L;
-        s[nt][0] = col < lim0 ? s[nt][0] * scale : -INFINITY;
-        s[nt][1] = col + 1 < lim0 ? s[nt][1] * scale : -INFINITY;
-        s[nt][2] = col < lim1 ? s[nt][2] * scale : -INFINITY;
-        s[nt][3] = col + 1 < lim1 ? s[nt][3] * scale : -INFINITY;
-        mx0 = fmaxf(mx0, fmaxf(s[nt][0], s[nt][1]));
-        mx1 = fmaxf(mx1, fmaxf(s[nt][2], s[nt][3]));
-      }
-      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
-      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
-      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
-      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
-      const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);  // finite: key block 0 always holds a valid key (col 0)
-      const float a0 = __expf(m0 - mn0), a1 = __expf(m1 - mn1);
-      l0 *= a0; l1 *= a1;
-#pragma unroll
-      for (int nt = 0; nt < 8; ++nt) { o[nt][0] *= a0; o[nt][1] *= a0; o[nt][2] *= a1; o[nt][3] *= a1; }
-#pragma unroll
-      for (int nt = 0; nt < 8; ++nt) {
-        s[nt][0] = __expf(s[nt][0] - mn0);
-        s[nt][1] = __expf(s[nt][1] - mn0);
-        s[nt][2] = __expf(s[nt][2] - mn1);
-        s[nt][3] = __expf(s[nt][3] - mn1);
-        l0 += s[nt][0] + s[nt][1];
-        l1 += s[nt][2] + s[nt][3];
-      }
-      m0 = mn0; m1 = mn1;
-#pragma unroll
-      for (int kk = 0; kk < 4; ++kk) {
-        uint32_t pa[4];
-        pa[0] = pack2_bf16(s[2 * kk][0], s[2 * kk][1]);
-        pa[1] = pack2_bf16(s[2 * kk][2], s[2 * kk][3]);
-        pa[2] = pack2_bf16(s[2 * kk + 1][0], s[2 * kk + 1][1]);
-        pa[3] = pack2_bf16(s[2 * kk + 1][2], s[2 * kk + 1][3]);
-#pragma unroll
-        for (int nt = 0; nt < 8; nt += 2) {
-          // four 8x8 blocks of V: (keys 16kk + {0,8}) x (dims 8nt + {0,8}); lane l addresses row l%8 of block l/8.
-          // .trans hands thread (g,t) the pairs V[key 2t, 2t+1][dim g] = the col-major B fragment of m16n8k16.
-          const int blk = lane >> 3;
-          const __nv_bfloat16* vr = Vs + (kb * 64 + 16 * kk + (blk & 1) * 8 + (lane & 7)) * kAttnKStride +
-                                    (nt + (blk >> 1)) * 8;
-          uint32_t b0, b1, b2, b3;
-          asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
-                       : "=r"(b0), "=r"(b1), "=r"(b2), "=r"(b3)
-                       : "r"(static_cast<uint32_t>(__cvta_generic_to_shared(vr))));
-          mma_bf16_16816(o[nt], pa, b0, b1);
-          mma_bf16_16816(o[nt + 1], pa, b2, b3);
-        }
-      }
-    }
-    l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
-    l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
-    l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
-    l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
-    const float i0 = 1.0f / l0, i1 = 1.0f / l1;
-    if (r0 < L) {
-      __nv_bfloat16* orow = out + (row0 + r0) * d + h * 64 + 2 * t;
-#pragma unroll
-      for (int nt = 0; nt < 8; ++nt)
-        *reinterpret_cast<uint32_t*>(orow + nt * 8) = pack2_bf16(o[nt][0] * i0, o[nt][1] * i0);
-    }
-    if (r1 < L) {
-      __nv_bfloat16* orow = out + (row0 + r1) * d + h * 64 + 2 * t;
-#pragma unroll
-      for (int nt = 0; nt < 8; ++nt)
-        *reinterpret_cast<uint32_t*>(orow + nt * 8) = pack2_bf16(o[nt][2] * i1, o[nt][3] * i1);
-    }
-  }
+__device__ __forceinline__ float fast_exp2(float x) {  // ex2.approx: 2 ulp, exp2(-inf) = 0
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
 }
+
+constexpr int kAttnKStride = 72;  // bf16 elements per K row in smem (64 + 8 pad: conflict-free fragments)
 
 // ---- short sequences (L <= 64: ViT-B/32 has 50 tokens): persistent CTAs, double-buffered cp.async staging ----------
 // The one-item-per-CTA kernel above is latency-bound at L = 50 (every CTA pays its global round trips with 16 warps
@@ -359,12 +228,6 @@ __device__ __forceinline__ void ldmatrix_x4_trans(uint32_t (&r)[4], const void* 
   asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
                : "r"(static_cast<uint32_t>(__cvta_generic_to_shared(smem_src))));
-}
-
-__device__ __forceinline__ float fast_exp2(float x) {  // ex2.approx: 2 ulp, exp2(-inf) = 0
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
 }
 
 __global__ void __launch_bounds__(128)
@@ -502,6 +365,156 @@ attention_short_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __r
   }
 }
 
+// ---- long sequences (L > 64: 197 tokens ViT-B/16, 257 ViT-L/14, 77 text tower) --------------------------------------
+// One CTA (8 warps) per (head, sequence): K and V of the head are staged once with cp.async ([Lp][72] bf16 each); every
+// warp walks 16-query tiles: the Q tile goes through a per-warp [16][72] staging buffer (coalesced 16-B loads ->
+// ldmatrix A fragments), the flash loop runs over 64-key blocks with K fragments from ldmatrix and V from
+// ldmatrix.trans, the softmax works in the exp2 domain, and O leaves through the same per-warp buffer as whole rows.
+// `causal`: row r attends keys <= r (clip/model.py build_attention_mask); key blocks entirely above the diagonal of a
+// query tile are skipped.
+constexpr int kAttnLongWarps = 8;
+
+__global__ void __launch_bounds__(kAttnLongWarps * 32, 2)
+attention_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, int L, int d,
+                 float scale_log2e, int causal) {
+  pdl_launch_dependents();
+  pdl_wait();
+  extern __shared__ __align__(16) uint8_t attn_smem[];
+  const int h = blockIdx.x, b = blockIdx.y;
+  const int Lp = (L + 63) & ~63;
+  __nv_bfloat16* Ks = reinterpret_cast<__nv_bfloat16*>(attn_smem);  // [Lp][72]
+  __nv_bfloat16* Vs = Ks + Lp * kAttnKStride;                       // [Lp][72]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  __nv_bfloat16* Qw = Vs + Lp * kAttnKStride + warp * 16 * kAttnKStride;  // this warp's [16][72] Q / O staging tile
+  const size_t row0 = static_cast<size_t>(b) * L;
+  const int ld = 3 * d;
+  {
+    const int c = threadIdx.x & 7;
+    const __nv_bfloat16* src = qkv + row0 * ld + h * 64 + c * 8;
+    for (int r = threadIdx.x >> 3; r < Lp; r += kAttnLongWarps * 4) {
+      __nv_bfloat16* kd = Ks + r * kAttnKStride + c * 8;
+      __nv_bfloat16* vd = Vs + r * kAttnKStride + c * 8;
+      if (r < L) {
+        cp_async16(kd, src + static_cast<size_t>(r) * ld + d);
+        cp_async16(vd, src + static_cast<size_t>(r) * ld + 2 * d);
+      } else {
+        *reinterpret_cast<uint4*>(kd) = make_uint4(0, 0, 0, 0);
+        *reinterpret_cast<uint4*>(vd) = make_uint4(0, 0, 0, 0);
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+  }
+  __syncthreads();
+
+  const int num_mt = (L + 15) >> 4;
+  for (int mt = warp; mt < num_mt; mt += kAttnLongWarps) {
+    const int m0 = mt * 16;
+    // ---- Q tile -> staging -> A fragments
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int u = i * 32 + lane, r = u >> 3, c = u & 7;
+      uint4 q4 = make_uint4(0, 0, 0, 0);
+      if (m0 + r < L) q4 = *reinterpret_cast<const uint4*>(qkv + (row0 + m0 + r) * ld + h * 64 + c * 8);
+      *reinterpret_cast<uint4*>(Qw + r * kAttnKStride + c * 8) = q4;
+    }
+    __syncwarp();
+    uint32_t qa[4][4];
+#pragma unroll
+    for (int kk = 0; kk < 4; ++kk)
+      ldmatrix_x4(qa[kk], Qw + ((lane & 7) + ((lane >> 3) & 1) * 8) * kAttnKStride + 16 * kk + (lane >> 4) * 8);
+    const int r0 = m0 + g, r1 = r0 + 8;
+    const int lim0 = causal ? min(L, r0 + 1) : L, lim1 = causal ? min(L, r1 + 1) : L;  // keys visible to each row
+    float o[8][4];
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) { o[nt][0] = o[nt][1] = o[nt][2] = o[nt][3] = 0.f; }
+    float mx0 = -INFINITY, mx1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+    const int kb_end = causal ? min(Lp / 64, (m0 + 15) / 64 + 1) : Lp / 64;
+    for (int kb = 0; kb < kb_end; ++kb) {
+      float s[8][4];
+#pragma unroll
+      for (int nt = 0; nt < 8; nt += 2) {
+        s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+        s[nt + 1][0] = s[nt + 1][1] = s[nt + 1][2] = s[nt + 1][3] = 0.f;
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+          uint32_t kf[4];
+          ldmatrix_x4(kf, Ks + (kb * 64 + (nt + (lane >> 4)) * 8 + (lane & 7)) * kAttnKStride + 16 * kk +
+                              ((lane >> 3) & 1) * 8);
+          mma_bf16_16816(s[nt], qa[kk], kf[0], kf[1]);
+          mma_bf16_16816(s[nt + 1], qa[kk], kf[2], kf[3]);
+        }
+      }
+      float bm0 = -INFINITY, bm1 = -INFINITY;
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        const int col = kb * 64 + nt * 8 + 2 * t;
+        s[nt][0] = col < lim0 ? s[nt][0] * scale_log2e : -INFINITY;
+        s[nt][1] = col + 1 < lim0 ? s[nt][1] * scale_log2e : -INFINITY;
+        s[nt][2] = col < lim1 ? s[nt][2] * scale_log2e : -INFINITY;
+        s[nt][3] = col + 1 < lim1 ? s[nt][3] * scale_log2e : -INFINITY;
+        bm0 = fmaxf(bm0, fmaxf(s[nt][0], s[nt][1]));
+        bm1 = fmaxf(bm1, fmaxf(s[nt][2], s[nt][3]));
+      }
+      bm0 = fmaxf(bm0, __shfl_xor_sync(0xffffffffu, bm0, 1));
+      bm0 = fmaxf(bm0, __shfl_xor_sync(0xffffffffu, bm0, 2));
+      bm1 = fmaxf(bm1, __shfl_xor_sync(0xffffffffu, bm1, 1));
+      bm1 = fmaxf(bm1, __shfl_xor_sync(0xffffffffu, bm1, 2));
+      const float mn0 = fmaxf(mx0, bm0), mn1 = fmaxf(mx1, bm1);  // finite: key block 0 always holds key 0
+      const float a0 = fast_exp2(mx0 - mn0), a1 = fast_exp2(mx1 - mn1);
+      l0 *= a0; l1 *= a1;
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) { o[nt][0] *= a0; o[nt][1] *= a0; o[nt][2] *= a1; o[nt][3] *= a1; }
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        s[nt][0] = fast_exp2(s[nt][0] - mn0);
+        s[nt][1] = fast_exp2(s[nt][1] - mn0);
+        s[nt][2] = fast_exp2(s[nt][2] - mn1);
+        s[nt][3] = fast_exp2(s[nt][3] - mn1);
+        l0 += s[nt][0] + s[nt][1];
+        l1 += s[nt][2] + s[nt][3];
+      }
+      mx0 = mn0; mx1 = mn1;
+#pragma unroll
+      for (int kk = 0; kk < 4; ++kk) {
+        uint32_t pa[4];
+        pa[0] = pack2_bf16(s[2 * kk][0], s[2 * kk][1]);
+        pa[1] = pack2_bf16(s[2 * kk][2], s[2 * kk][3]);
+        pa[2] = pack2_bf16(s[2 * kk + 1][0], s[2 * kk + 1][1]);
+        pa[3] = pack2_bf16(s[2 * kk + 1][2], s[2 * kk + 1][3]);
+#pragma unroll
+        for (int nt = 0; nt < 8; nt += 2) {
+          uint32_t vb[4];
+          ldmatrix_x4_trans(vb, Vs + (kb * 64 + 16 * kk + ((lane >> 3) & 1) * 8 + (lane & 7)) * kAttnKStride +
+                                    (nt + (lane >> 4)) * 8);
+          mma_bf16_16816(o[nt], pa, vb[0], vb[1]);
+          mma_bf16_16816(o[nt + 1], pa, vb[2], vb[3]);
+        }
+      }
+    }
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+    const float i0 = 1.0f / l0, i1 = 1.0f / l1;
+    __syncwarp();  // every lane's ldmatrix of the Q tile is done: the buffer now carries O
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) {
+      *reinterpret_cast<uint32_t*>(Qw + g * kAttnKStride + nt * 8 + 2 * t) = pack2_bf16(o[nt][0] * i0, o[nt][1] * i0);
+      *reinterpret_cast<uint32_t*>(Qw + (g + 8) * kAttnKStride + nt * 8 + 2 * t) = pack2_bf16(o[nt][2] * i1, o[nt][3] * i1);
+    }
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int u = i * 32 + lane, r = u >> 3, c = u & 7;
+      if (m0 + r < L)
+        *reinterpret_cast<uint4*>(out + (row0 + m0 + r) * d + h * 64 + c * 8) =
+            *reinterpret_cast<const uint4*>(Qw + r * kAttnKStride + c * 8);
+    }
+    __syncwarp();  // the staging tile is rewritten by the next query tile
+  }
+}
+
 int launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int d, int heads, int causal,
                      cudaStream_t stream) {
   EVR_REQUIRE(heads * 64 == d, "attention: head dim must be 64 (d=%d heads=%d)", d, heads);
@@ -521,7 +534,7 @@ int launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L,
     return 0;
   }
   const int Lp = (L + 63) & ~63;
-  const size_t smem = 2 * static_cast<size_t>(Lp) * kAttnKStride * 2;  // K and V, [Lp][72] bf16 each
+  const size_t smem = (2 * static_cast<size_t>(Lp) + kAttnLongWarps * 16) * kAttnKStride * 2;  // K, V, per-warp Q/O tiles
   EVR_REQUIRE(smem <= 200 * 1024, "attention: sequence %d too long for the single-CTA K/V staging", L);
   static size_t configured = 0;
   if (smem > 48 * 1024 && smem > configured) {
@@ -530,7 +543,8 @@ int launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L,
     configured = smem;
   }
   ProfScope ps(PF_ATTN, stream);
-  EVR_CHECK_CUDA(launch_pdl(attention_kernel, dim3(dim3(heads, B)), dim3(128), smem, stream, qkv, out, L, d, 0.125f, causal));
+  EVR_CHECK_CUDA(launch_pdl(attention_kernel, dim3(heads, B), dim3(kAttnLongWarps * 32), smem, stream, qkv, out, L, d,
+                            0.125f * 1.4426950408889634f, causal));
   EVR_CHECK_LAUNCH();
   return 0;
 }
