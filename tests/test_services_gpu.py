@@ -193,3 +193,40 @@ def test_clip_face_and_legacy_ingest(tmp_path, cuda, visual, full_sd):
     rows = np.load(path)
     assert rows.shape == (3, 512) and rows.dtype == np.float16
     assert np.linalg.norm(rows.astype(np.float32), axis=-1).min() > 2.0   # not normalised (embedding.py:55)
+
+
+def test_text_query_strategies(tmp_path, cuda, full_sd):
+    """query_strategies.query_by_text_clip / _with_adaptive_threshold over the service callbacks (a12): candidates =
+    top_k*3 of the scan, joined to metadata by frameidx, scored by extract_query_confidence, best top_k returned."""
+    qs = importlib.import_module(PKG + ".query_strategies")
+    rng = np.random.default_rng(21)
+    vec = rng.standard_normal((1, 512)).astype(np.float32)
+    svc, ps = _site(tmp_path, full_sd, {"vid": ["0.png"]}, text_encoder=lambda q: vec)
+    raw = rng.standard_normal((400, 512)).astype(np.float32)
+    np.save(ps.get_embeddings_path("vid"), raw)
+    items = [{"filepath": f"/x/vid/{i}.jpg", "frameidx": i, "tag": f"t{i}"} for i in range(400)]
+    items.append({"filepath": "/x/vid/dup.jpg", "frameidx": 5, "tag": "second record with frameidx 5"})
+    json.dump(items[:400], open(ps.get_metadata_path("vid"), "w"))
+    fmt = lambda rec: {"id": rec["frameidx"], "title": rec["tag"], "confidence": rec["clip_similarity"]}
+    emb = so.normalise_store(raw)
+    q = vec / np.linalg.norm(vec)
+    sim = (emb @ q.T).ravel()
+    order = np.argsort(-sim)
+    out = qs.query_by_text_clip("người đang chạy", 10, svc.search_top_frames, svc.extract_query_confidence, fmt, "vid",
+                                ps.video_data_mapping)
+    assert [e["id"] for e in out] == order[:10].tolist()
+    assert all(abs(e["clip_similarity"] - sim[e["id"]]) < 2 * EPS and e["confidence"] == e["clip_similarity"] for e in out)
+    assert all(a["clip_similarity"] >= b["clip_similarity"] for a, b in zip(out, out[1:]))
+    thr = float(sim[order[4]]) - 1e-4                               # five frames pass the threshold
+    out = qs.query_by_text_with_adaptive_threshold("q", thr, 10, svc.search_top_frames, svc.extract_query_confidence,
+                                                   fmt, "vid", ps.video_data_mapping)
+    assert [e["id"] for e in out] == order[:5].tolist()
+    # unknown video + no default metadata file -> [] (errors never propagate)
+    qs.METADATA_DIR = str(tmp_path / "nowhere")
+    assert qs.query_by_text_clip("q", 5, svc.search_top_frames, svc.extract_query_confidence, fmt, "other", {}) == []
+    qs.text_processor = lambda s: s.upper()
+    seen = []
+    qs.query_by_text_clip("abc", 2, lambda t, k, v: seen.append((t, k)) or [], svc.extract_query_confidence, fmt, "vid",
+                          ps.video_data_mapping)
+    qs.text_processor = None
+    assert seen == [("ABC", 6)]                                     # processed text, top_k * 3 candidates
