@@ -105,3 +105,58 @@ def query_by_text_with_adaptive_threshold(query, adaptive_threshold, top_k, sear
     except Exception as e:
         print(f"Error in query_by_text_with_adaptive_threshold: {e}")
         return []
+
+
+def search_by_image(embedding_service, image_url, adaptive_threshold, top_k, format_event_for_frontend, video_name=None,
+                    video_data_mapping=None):
+    """Image-query path (Backend/services/search_service.py:611-705): encode the query image,
+    scan with `top_k * 3`, keep candidates whose cosine passes `adaptive_threshold`, best `top_k` events.
+
+    `image_url`: file path, `data:image/...;base64,` URL, or a PIL image (http(s) URLs need the network and are
+    refused).  Difference from the reference: a candidate's similarity is the scan's own score -- the same
+    dot product of its store row with the query -- instead of re-embedding the frame with
+    `extract_image_embedding(<basename>)`, which fails outside the frames directory and silently drops the candidate
+    (search_service.py:679)."""
+    try:
+        import base64
+        from io import BytesIO
+
+        import numpy as np
+        import torch
+        from PIL import Image
+        if hasattr(image_url, "convert"):
+            img = image_url.convert('RGB')
+        elif image_url.startswith(('http://', 'https://')):
+            raise RuntimeError("remote image URLs need network access")
+        elif image_url.startswith('data:image'):
+            img = Image.open(BytesIO(base64.b64decode(image_url.split(',')[1]))).convert('RGB')
+        else:
+            img = Image.open(image_url).convert('RGB')
+        svc = embedding_service
+        image = svc.preprocess(img).unsqueeze(0).to(svc.device)
+        with torch.no_grad():
+            if svc.get_active_model_name() == "finetuned" and svc.finetuned_model is not None:
+                feats = svc.finetuned_model(image)
+            else:
+                feats = svc.original_model.encode_image(image)
+            feats = feats.float()
+            feats = (feats / feats.norm(dim=-1, keepdim=True)).cpu().numpy()
+        table = _metadata_by_frameidx(get_video_metadata_path(video_name, video_data_mapping))
+        results = []
+        for frame_name, similarity in svc.search_with_scores(feats, top_k * 3, video_name):
+            try:
+                frame_data = table.get(int(Path(frame_name).stem))
+                if frame_data and similarity >= adaptive_threshold:
+                    rec = frame_data.copy()
+                    rec['clip_similarity'] = float(similarity)
+                    event = format_event_for_frontend(rec)
+                    event["clip_similarity"] = float(similarity)
+                    event["confidence"] = float(similarity)
+                    results.append(event)
+            except Exception as e:
+                print(f"Error processing frame {frame_name}: {e}")
+        results.sort(key=lambda x: x.get("clip_similarity", 0), reverse=True)
+        return results[:top_k]
+    except Exception as e:
+        print(f"Error in image search: {e}")
+        return []

@@ -230,3 +230,30 @@ def test_text_query_strategies(tmp_path, cuda, full_sd):
                           ps.video_data_mapping)
     qs.text_processor = None
     assert seen == [("ABC", 6)]                                     # processed text, top_k * 3 candidates
+
+
+def test_search_by_image(tmp_path, cuda, visual, full_sd):
+    """a15: query by image = encode -> scan(top_k*3) -> threshold -> top_k; a frame of the video finds itself first."""
+    qs = importlib.import_module(PKG + ".query_strategies")
+    names = [f"{i}.png" for i in range(12)]
+    svc, ps = _site(tmp_path, full_sd, {"vid": names})
+    folder = ps.video_data_mapping["vid"]["frames_dir"]
+    assert svc.extract_and_save_embeddings_from_folder(folder, None, "vid") is not None
+    fmt = lambda rec: {"id": rec["frameidx"]}
+    query = os.path.join(folder, "7.png")
+    out = qs.search_by_image(svc, query, -1.0, 3, fmt, "vid", ps.video_data_mapping)
+    assert len(out) == 3 and out[0]["id"] == 7 and abs(out[0]["clip_similarity"] - 1.0) < 4e-3
+    assert out[0]["confidence"] == out[0]["clip_similarity"]
+    assert all(a["clip_similarity"] >= b["clip_similarity"] for a, b in zip(out, out[1:]))
+    # oracle: cosines of the query frame's fp32 embedding against the stored rows, ranks up to near-ties
+    order = sorted(names)
+    ref = _oracle_rows(visual, svc, folder, order)
+    sim = ref @ ref[order.index("7.png")]
+    assert abs(out[1]["clip_similarity"] - np.sort(sim)[-2]) < 4e-3
+    only_self = qs.search_by_image(svc, query, float(np.sort(sim)[-2]) + 0.5 * (1 - float(np.sort(sim)[-2])), 3, fmt, "vid",
+                                   ps.video_data_mapping)
+    assert [e["id"] for e in only_self] == [7]
+    from PIL import Image
+    assert qs.search_by_image(svc, Image.open(query), -1.0, 1, fmt, "vid", ps.video_data_mapping)[0]["id"] == 7
+    assert qs.search_by_image(svc, "http://example.com/x.jpg", 0.0, 3, fmt, "vid", ps.video_data_mapping) == []
+    assert qs.search_by_image(svc, str(tmp_path / "missing.jpg"), 0.0, 3, fmt, "vid", ps.video_data_mapping) == []
