@@ -114,7 +114,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   if constexpr (CG == 2) rank = cluster_ctarank();
   const bool leader = rank == 0;
   const int unit = blockIdx.x / CG, num_units = gridDim.x / CG;
-  if constexpr (CG == 2) cluster_sync_all();  // both CTAs resident before the pair-wide TMEM allocation
+  if constexpr (CG == 2) cluster_sync_relaxed();  // both CTAs resident before the pair-wide TMEM allocation
   const int num_n = (args.N + BLOCK_N - 1) / BLOCK_N;
   const int num_tiles = num_m * num_n;
   const int num_kb = args.K / kGemmBlockK;
@@ -139,8 +139,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     else tmem_alloc<Cfg::kTmemCols>(tmem_slot);
   }
   tc_fence_before();
-  if constexpr (CG == 2) cluster_sync_all();
-  else __syncthreads();
+  __syncthreads();  // CTA-local visibility of the barrier inits and of the TMEM base address
+  if constexpr (CG == 2) cluster_sync_relaxed();  // peer's barriers initialised (fence.mbarrier_init) before remote arrives
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   pdl_wait();  // everything above overlapped the previous kernel's tail; activations are touched only below

@@ -183,6 +183,13 @@ __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
   asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
+// Execution-only cluster barrier (no release fence): used where the data published across the barrier is already
+// ordered by its own fence (fence.mbarrier_init.release.cluster for barrier inits, tcgen05.fence for TMEM state) --
+// the release form costs a MEMBAR.ALL.GPU per kernel prologue.
+__device__ __forceinline__ void cluster_sync_relaxed() {
+  asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.aligned;" ::: "memory");
+}
 constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;  // shared::cluster address of the same offset in cluster rank 0
 
 template <uint32_t kCols>
