@@ -3,7 +3,7 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libevr.so")
+LIB_PATH = os.environ.get("EVR_LIB_PATH") or os.path.join(_HERE, "lib", "libevr.so")  # override: A/B builds
 
 
 class EvrError(RuntimeError):

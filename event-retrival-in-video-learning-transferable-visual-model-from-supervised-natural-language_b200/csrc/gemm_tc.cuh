@@ -49,7 +49,8 @@ struct EpiCfg {
   static constexpr int kRowBytes = kEpiCols * kElt;       // 64 | 128
   static constexpr int kPitch = kRowBytes + 16;           // 80 | 144
   static constexpr int kWarpBytes = 32 * kPitch;
-  static constexpr int kBytes = 8 * kWarpBytes;           // 20 480 | 36 864
+  static constexpr int kBiasWarpBytes = 4 * 32 * 4;       // bias of this warp's <= 4 chunks x 32 columns
+  static constexpr int kBytes = 8 * (kWarpBytes + kBiasWarpBytes);  // 24 576 | 40 960
   static constexpr int kUnitsPerRow = kRowBytes / 16;     // 4 | 8
 };
 
@@ -217,6 +218,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     constexpr int kChunks = BLOCK_N / 64;  // 32-column chunks per warp
     uint8_t* stage = smem_epi + ew * Epi::kWarpBytes;
     uint8_t* my_row = stage + lane * Epi::kPitch;
+    float* bias_s = reinterpret_cast<float*>(smem_epi + 8 * Epi::kWarpBytes + ew * Epi::kBiasWarpBytes);
     constexpr int kColsPerUnit = 16 / Epi::kElt;
     constexpr int kIters = Epi::kUnitsPerRow;  // 16-B units per lane per chunk: 4 (bf16) | 8 (fp32)
     int as = 0;
@@ -225,6 +227,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       const int n_idx = tile % num_n, m_idx = tile / num_n;  // n-fast: the N tiles of one row block run together, A is read from HBM once
       const int row0 = m_idx * kTileM + static_cast<int>(rank) * kGemmBlockM + q * 32;  // first row of this warp
       const int col_base = n_idx * BLOCK_N + hsel * kEpiCols;
+      // this tile's bias values for the warp's columns go to shared memory while the MMAs are still running; the chunk
+      // loop then reads them as broadcast ld.shared (a global/L2 round trip per chunk sat on the critical path: ncu
+      // showed the bias FADDs as the top long_scoreboard stall of the epilogue)
+      if (args.bias != nullptr) {
+        if (lane < kChunks * 8) {
+          const int col = col_base + (lane >> 3) * 64 + (lane & 7) * 4;
+          float4 bb = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (col < args.N) bb = __ldg(reinterpret_cast<const float4*>(args.bias + col));
+          *reinterpret_cast<float4*>(bias_s + lane * 4) = bb;
+        }
+        __syncwarp();
+      }
       mbar_wait(&tmem_full[as], aphase);
       tc_fence_after();
       uint32_t v[2][32];
@@ -250,10 +264,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 #pragma unroll
           for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[c & 1][j]);
           if (args.bias != nullptr) {
-            const float4* b4 = reinterpret_cast<const float4*>(args.bias + col0);
+            const float4* b4 = reinterpret_cast<const float4*>(bias_s + c * 32);
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-              const float4 bb = __ldg(b4 + j);
+              const float4 bb = b4[j];
               f[4 * j] += bb.x; f[4 * j + 1] += bb.y; f[4 * j + 2] += bb.z; f[4 * j + 3] += bb.w;
             }
           }
