@@ -94,3 +94,34 @@ def current_stream_ptr():
 def ptr(t):
     """Device (or host) pointer of a torch tensor as c_void_p; None -> NULL."""
     return c_void_p(0 if t is None else t.data_ptr())
+
+
+class HandleGuard:
+    """Serialises use of one native handle's device workspace across host threads AND CUDA streams.
+
+    The reference runs under a threaded Flask server and holds no locks; a handle here owns one set of
+    activation / candidate buffers, so two calls must not overlap on the device even when they come from different
+    streams: the guard takes a host lock for the enqueue and makes the caller's stream wait for the previous call's
+    completion event before the kernels that reuse the workspace are launched."""
+
+    def __init__(self):
+        import threading
+        self._lock = threading.Lock()
+        self._done = None
+
+    def __enter__(self):
+        import torch
+        self._lock.acquire()
+        if self._done is not None:
+            torch.cuda.current_stream().wait_event(self._done)
+        return self
+
+    def __exit__(self, *exc):
+        import torch
+        try:
+            if self._done is None:
+                self._done = torch.cuda.Event()
+            self._done.record(torch.cuda.current_stream())
+        finally:
+            self._lock.release()
+        return False

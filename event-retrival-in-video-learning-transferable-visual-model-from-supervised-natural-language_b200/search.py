@@ -13,7 +13,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import lib, check, ptr, current_stream_ptr
+from ._lib import HandleGuard, lib, check, ptr, current_stream_ptr
 
 MAX_FUSED_K = 1024
 
@@ -39,6 +39,7 @@ class FrameStore:
         self.row_offset = int(row_offset)
         self.device = rows_fp16.device
         self._ws = None
+        self._guard = HandleGuard()  # the candidate workspace is shared by every search on this store
 
     # ---- construction -------------------------------------------------------------------------
     @classmethod
@@ -93,7 +94,7 @@ class FrameStore:
             return self._search_large_k(q, k_eff)
         out_s = torch.empty((Q, k_eff), dtype=torch.float32, device=self.device)
         out_i = torch.empty((Q, k_eff), dtype=torch.int64, device=self.device)
-        with torch.cuda.device(self.device):
+        with torch.cuda.device(self.device), self._guard:
             ws = self._workspace(Q, k_eff)
             check(lib.evr_topk_search(ptr(self.rows), self.N, self.D, self.row_offset, ptr(q), Q, k_eff, ptr(out_s),
                                       ptr(out_i), ptr(ws), ws.numel(), current_stream_ptr()), "evr_topk_search")

@@ -10,7 +10,7 @@ import ctypes
 
 import torch
 
-from ._lib import lib, check, ptr, current_stream_ptr, TextCfg
+from ._lib import HandleGuard, lib, check, ptr, current_stream_ptr, TextCfg
 
 
 def text_weight_keys(layers):
@@ -50,6 +50,7 @@ class TextEncoder:
                   "evr_text_create")
             torch.cuda.synchronize()
         self._h = handle
+        self._guard = HandleGuard()
 
     @classmethod
     def from_state_dict(cls, sd, device="cuda", max_batch=64):
@@ -85,7 +86,7 @@ class TextEncoder:
         t = t.to(torch.int32).contiguous()
         out = torch.empty((B, self.out_dim), dtype=out_dtype, device=self.device)
         if B:
-            with torch.cuda.device(self.device):
+            with torch.cuda.device(self.device), self._guard:
                 check(lib.evr_text_encode(self._h, ptr(t), B, ptr(out), 0 if out_dtype == torch.float32 else 1,
                                           1 if normalise else 0, current_stream_ptr()), "evr_text_encode")
         return out

@@ -9,7 +9,7 @@ import ctypes
 
 import torch
 
-from ._lib import lib, check, ptr, current_stream_ptr, VitCfg
+from ._lib import HandleGuard, lib, check, ptr, current_stream_ptr, VitCfg
 
 GEOMETRY = {  # clip/model.py build_model
     "ViT-B/32": dict(image_size=224, patch=32, width=768, layers=12, heads=12, out_dim=512),
@@ -46,6 +46,7 @@ class VisionEncoder:
                   "evr_vit_create")
             torch.cuda.synchronize()
         self._h = handle
+        self._guard = HandleGuard()
 
     @classmethod
     def from_state_dict(cls, sd, name="ViT-B/32", device="cuda", max_batch=256, prefix=""):
@@ -84,7 +85,7 @@ class VisionEncoder:
         B = pix.shape[0]
         out = torch.empty((B, self.out_dim), dtype=out_dtype, device=self.device)
         if B:
-            with torch.cuda.device(self.device):
+            with torch.cuda.device(self.device), self._guard:
                 check(lib.evr_vit_encode(self._h, ptr(pix), pix_dtype, B, ptr(out),
                                          0 if out_dtype == torch.float32 else 1, 1 if normalise else 0,
                                          current_stream_ptr()), "evr_vit_encode")
