@@ -141,12 +141,38 @@ def barrier_sync(world):
     torch.cuda.synchronize()
 
 
+def bench_encode_other(pkg, dev, name, batch, steps, warmup, peaks):
+    """Secondary line: another tower geometry (BASELINE config 5 is ViT-L/14) on rank 0's GPU, device-resident frames."""
+    import torch
+    sd = pkg.clip.random_visual_state_dict(name, seed=1)
+    enc = pkg.vit.VisionEncoder.from_state_dict(sd, name, device=dev, max_batch=batch, prefix="visual.")
+    g = torch.Generator(device="cpu").manual_seed(7)
+    frames = [torch.randint(0, 256, (batch, 224, 224, 3), generator=g, dtype=torch.uint8).to(dev) for _ in range(4)]
+    for i in range(warmup):
+        enc.encode(frames[i % 4], normalise=True)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for i in range(steps):
+        enc.encode(frames[i % 4], normalise=True)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    total_flops, _ = vit_flops_per_frame(name)
+    tf = total_flops * batch / (ms * 1e-3) / 1e12
+    return {"metric": f"frames/s {name} encode", "unit": "frames/s", "value": round(batch / ms * 1e3, 1),
+            "ms_per_step": round(ms, 4), "steps": steps, "warmup": warmup, "n_gpus": 1,
+            "config": {"workload": f"{name} keyframe encoding, batch {batch} synthetic 224x224 frames, bf16, one GPU"},
+            "whole_step_frac": round(tf / peaks["tf_sustained"], 4), "achieved_tflops": round(tf, 1)}
+
+
 # ----------------------------------------------------------------------------------------------- encode (ours)
-def bench_encode(pkg, vo, dev, rank, world, steps, warmup, batch, peaks):
+def bench_encode(pkg, dev, rank, world, steps, warmup, batch, peaks):
     import torch
     _lib = pkg._lib
-    visual = vo.build_visual(VIT_NAME, seed=1)  # seeded random init, openai scales (no weights on the box)
-    enc = pkg.vit.VisionEncoder.from_state_dict(visual.state_dict(), VIT_NAME, device=dev, max_batch=batch)
+    # seeded random init with openai's scales (no weights on the box); the product's own initialiser, not the oracle's
+    sd = pkg.clip.random_visual_state_dict(VIT_NAME, seed=1)
+    enc = pkg.vit.VisionEncoder.from_state_dict(sd, VIT_NAME, device=dev, max_batch=batch, prefix="visual.")
     # synthetic uint8 RGB frames (SURVEY.md 8d); R distinct batches so consecutive steps never reuse L2 lines
     R = 8
     g = torch.Generator(device="cpu").manual_seed(1000 + rank)
@@ -438,7 +464,7 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     import __graft_entry__ as ge
     pkg = ge.load_package()
-    from oracle import search_oracle as so, vit_oracle as vo  # vo: weight init + synthetic frames; so: cpu_baseline
+    from oracle import search_oracle as so, vit_oracle as vo  # cpu_baseline leg only (rank 0, N=1)
     peaks = load_peaks()
 
     line = {"metric": METRIC, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -448,7 +474,7 @@ def main():
                        "parallelism": f"dp{world}",
                        "l2": "8 distinct resident uint8 batches (308 MB) rotate; weights+activations exceed L2"}}
     if args.workload in ("both", "encode"):
-        r = bench_encode(pkg, vo, dev, rank, world, args.steps, args.warmup, args.batch, peaks)
+        r = bench_encode(pkg, dev, rank, world, args.steps, args.warmup, args.batch, peaks)
         line.update(value=round(r["value"], 1), ms_per_step=round(r["ms_per_step"], 4), e2e=r["e2e"],
                     gpu_launches=r["gpu_launches"], clocks=r["clocks"], roofline=r["roofline"])
     if args.workload in ("both", "search"):
@@ -460,6 +486,9 @@ def main():
             line.update(metric=s["metric"], unit=s["unit"], value=s["value"], ms_per_step=s["ms_per_step"],
                         steps=s["steps"], scaling=s["scaling"], dtype="f16", e2e=s["e2e"],
                         gpu_launches=s["gpu_launches"], roofline=s.get("roofline"), config=s["config"])
+    if rank == 0 and world == 1 and args.workload == "both":
+        # BASELINE config 5's tower (ViT-L/14, 768-d) as a secondary line: 8 steps of 128 frames, about one second
+        line["vit_l14"] = bench_encode_other(pkg, dev, "ViT-L/14", 128, 8, 3, peaks)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         fps, threads = cpu_encode(vo, n_batches=8)
         qps = cpu_search(so, 1_000_000, 4, args.k)

@@ -12,15 +12,14 @@ import __graft_entry__ as ge  # noqa: E402
 import bench  # noqa: E402
 
 pkg = ge.load_package()
-from oracle import vit_oracle as vo  # noqa: E402  (weight init + synthetic frames only)
 
 case = sys.argv[1]
 steps = int(sys.argv[2]) if len(sys.argv) > 2 else 2
 dev = torch.device("cuda:0")
 torch.cuda.set_device(dev)
 if case == "encode":
-    visual = vo.build_visual("ViT-B/32", seed=1)
-    enc = pkg.vit.VisionEncoder.from_state_dict(visual.state_dict(), "ViT-B/32", device=dev, max_batch=256)
+    sd = pkg.clip.random_visual_state_dict("ViT-B/32", seed=1)
+    enc = pkg.vit.VisionEncoder.from_state_dict(sd, "ViT-B/32", device=dev, max_batch=256, prefix="visual.")
     g = torch.Generator().manual_seed(0)
     frames = torch.randint(0, 256, (256, 224, 224, 3), generator=g, dtype=torch.uint8).to(dev)
     for _ in range(steps):

@@ -10,3 +10,6 @@ s = d.get("search")
 if s:
     print("search", s["value"], "q/s", s["ms_per_step"], "ms | e2e", s["e2e"]["value"], "| frac", s["roofline"]["frac"],
           [(h["Q"], h["frac_of_hbm_peak"]) for h in s.get("hbm_regime", [])])
+v = d.get("vit_l14")
+if v:
+    print("vit_l14", v["value"], "frames/s", v["ms_per_step"], "ms | whole-step frac", v["whole_step_frac"])
