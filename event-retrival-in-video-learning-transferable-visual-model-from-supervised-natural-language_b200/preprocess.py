@@ -27,11 +27,19 @@ def _bicubic(x):
                     np.where(x < 2.0, (((x - 5.0) * x + 8.0) * x - 4.0) * a, 0.0))
 
 
+def _bilinear(x):
+    x = np.abs(x)
+    return np.where(x < 1.0, 1.0 - x, 0.0)
+
+
+FILTERS = {"bicubic": (_bicubic, 2.0), "bilinear": (_bilinear, 1.0)}  # Resample.c BICUBIC / BILINEAR (filter, support)
+
+
 @functools.lru_cache(maxsize=256)
-def resample_coeffs(in_size, out_size):
-    """precompute_coeffs + normalize_coeffs_8bpc of Resample.c for the BICUBIC filter (support 2.0) over the full
-    input range [0, in_size).  -> (bounds int32 [out, 2] = (xmin, count), kk int32 [out, ksize])."""
-    support0 = 2.0
+def resample_coeffs(in_size, out_size, filt="bicubic"):
+    """precompute_coeffs + normalize_coeffs_8bpc of Resample.c for one axis over the full input range [0, in_size).
+    -> (bounds int32 [out, 2] = (xmin, count), kk int32 [out, ksize])."""
+    kernel, support0 = FILTERS[filt]
     scale = filterscale = float(in_size) / out_size
     if filterscale < 1.0:
         filterscale = 1.0
@@ -49,7 +57,7 @@ def resample_coeffs(in_size, out_size):
         if xmax > in_size:
             xmax = in_size
         xmax -= xmin
-        k = _bicubic((np.arange(xmax, dtype=np.float64) + xmin - center + 0.5) * ss)
+        k = kernel((np.arange(xmax, dtype=np.float64) + xmin - center + 0.5) * ss)
         ww = 0.0
         for v in k:            # sequential double accumulation, as the C loop
             ww += v
@@ -73,12 +81,23 @@ def crop_origin(w, h, n_px):
     return int(round((w - n_px) / 2.0)), int(round((h - n_px) / 2.0))
 
 
-def plan(w, h, n_px):
-    """Everything the two device passes need for a w x h source: tables restricted to the cropped window."""
-    rw, rh = resized_size(w, h, n_px)
-    left, top = crop_origin(rw, rh, n_px)
-    hb, hk = resample_coeffs(w, rw)
-    vb, vk = resample_coeffs(h, rh)
+def plan(w, h, n_px, mode="clip"):
+    """Everything the two device passes need for a w x h source: tables restricted to the output window.
+    mode "clip":    Resize(n_px, BICUBIC) + CenterCrop(n_px)   (clip._transform; the service's ingest)
+    mode "stretch": Resize((n_px, n_px)), torchvision's default BILINEAR, no crop
+                    (the evaluation harness, content/Test_compare_model/compare_models.py:37, :387)"""
+    if mode == "clip":
+        rw, rh = resized_size(w, h, n_px)
+        left, top = crop_origin(rw, rh, n_px)
+        filt = "bicubic"
+    elif mode == "stretch":
+        rw = rh = n_px
+        left = top = 0
+        filt = "bilinear"
+    else:
+        raise ValueError(f"unknown preprocessing mode {mode!r}")
+    hb, hk = resample_coeffs(w, rw, filt)
+    vb, vk = resample_coeffs(h, rh, filt)
     hb, hk = hb[left:left + n_px], hk[left:left + n_px]
     vb, vk = vb[top:top + n_px], vk[top:top + n_px]
     y0 = int(vb[:, 0].min())
@@ -94,8 +113,10 @@ class GpuPreprocess:
     accepted too) -> uint8 device tensor [B, n_px, n_px, 3], bit-identical to the PIL pipeline.  Feed it to
     `VisionEncoder.encode` / `model.encode_image`, which fuse ToTensor + Normalize."""
 
-    def __init__(self, n_px=224, device="cuda"):
+    def __init__(self, n_px=224, device="cuda", mode="clip"):
         self.n_px = int(n_px)
+        self.mode = mode
+        plan(n_px, n_px, n_px, mode)  # validates the mode
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise RuntimeError("GpuPreprocess runs on a CUDA device only (the host path is clip.load's preprocess)")
@@ -104,7 +125,7 @@ class GpuPreprocess:
     def _plan(self, w, h):
         key = (w, h)
         if key not in self._plans:
-            p = plan(w, h, self.n_px)
+            p = plan(w, h, self.n_px, self.mode)
             dev = {k: torch.from_numpy(p[k]).to(self.device) for k in ("hb", "hk", "vb", "vk")}
             self._plans[key] = (p, dev)
         return self._plans[key]

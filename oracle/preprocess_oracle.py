@@ -19,6 +19,13 @@ def pil_transform_u8(img, n_px=224):
     return np.asarray(T.CenterCrop(n_px)(T.Resize(n_px, interpolation=T.InterpolationMode.BICUBIC)(pil)))
 
 
+def pil_stretch_u8(img, n_px=224):
+    """transforms.Resize((n_px, n_px)) of the evaluation harness (compare_models.py:37, :387): bilinear, no crop."""
+    from PIL import Image
+    from torchvision import transforms as T
+    return np.asarray(T.Resize((n_px, n_px))(Image.fromarray(img)))
+
+
 def resample_reference_u8(img, p, n_px):
     """The two integer passes in numpy; `p` = preprocess.plan(w, h, n_px) (coefficient tables + row window)."""
     src = img.astype(np.int64)

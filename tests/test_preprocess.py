@@ -32,3 +32,15 @@ def test_geometry_rules():
     assert (b[:, 0] >= 0).all() and (b[:, 0] + b[:, 1] <= 448).all()
     b, k = pp.resample_coeffs(224, 224)
     assert ((k != 0).sum(1) == 1).all() and (k.max(1) == 1 << 22).all()         # identity scale: one unit tap per row
+
+
+@pytest.mark.parametrize("h,w", [(360, 640), (224, 224), (500, 333), (100, 160), (1080, 1920)])
+def test_stretch_mode_equals_torchvision_resize(h, w):
+    """compare_models.py's transform: Resize((224, 224)) = PIL bilinear with the support stretched by the scale."""
+    pp = importlib.import_module(PKG + ".preprocess")
+    rng = np.random.default_rng(h * 31 + w)
+    img = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+    out = po.resample_reference_u8(img, pp.plan(w, h, 224, "stretch"), 224)
+    assert np.array_equal(po.pil_stretch_u8(img, 224), out)
+    with pytest.raises(ValueError):
+        pp.plan(w, h, 224, "nearest")

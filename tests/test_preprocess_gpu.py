@@ -59,3 +59,13 @@ def test_preprocess_feeds_the_encoder(pkg, cuda):
     enc = pkg.vit.VisionEncoder.from_state_dict(visual.state_dict(), "ViT-B/32", device=cuda, max_batch=8)
     out = enc.encode(pkg.preprocess.GpuPreprocess(224, device=cuda)(img), normalise=True).cpu().numpy()
     assert ((out * ref).sum(-1)).min() >= 0.999
+
+
+@pytest.mark.parametrize("h,w", [(360, 640), (500, 333), (100, 160)])
+def test_stretch_mode_is_bit_exact(pkg, cuda, h, w):
+    """The evaluation harness' transform (compare_models.py:37: Resize((224, 224)), bilinear) on the device."""
+    pre = pkg.preprocess.GpuPreprocess(224, device=cuda, mode="stretch")
+    img = _frames(3, h, w, h * w)
+    out = pre(img).cpu().numpy()
+    for i in range(3):
+        assert np.array_equal(out[i], po.pil_stretch_u8(img[i], 224))
