@@ -50,6 +50,19 @@ int make_tmap_2d_16b(CUtensorMap* out, const void* base, uint64_t rows, uint64_t
 
 int sm_count();
 
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is per device: a call site remembers the largest size it has
+// configured on each device (one process per GPU is the design, but a process that touches several GPUs must work).
+struct PerDeviceMax {
+  int v[64] = {};
+  bool needs(int want) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    dev &= 63;
+    if (want > v[dev]) { v[dev] = want; return true; }
+    return false;
+  }
+};
+
 // Programmatic dependent launch (PDL): kernels of one encode are launched with programmatic stream serialisation, so
 // a kernel's CTAs become resident -- and run their prologue (barrier init, TMEM allocation, descriptor prefetch) --
 // while the previous kernel drains; `pdl_wait()` blocks until that previous grid has completed and flushed its

@@ -13,11 +13,9 @@ static int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const GemmAr
                       cudaStream_t stream) {
   using Cfg = GemmCfg<BLOCK_N, EPI, CG>;
   auto kern = gemm_tc_kernel<BLOCK_N, EPI, CG>;
-  static bool attr_set = false;  // per instantiation
-  if (!attr_set) {
+  static PerDeviceMax configured;  // per instantiation
+  if (configured.needs(Cfg::kSmemBytes))
     EVR_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
-    attr_set = true;
-  }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(grid);
   cfg.blockDim = dim3(kGemmThreads);

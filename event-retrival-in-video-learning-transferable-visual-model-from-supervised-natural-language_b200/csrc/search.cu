@@ -779,10 +779,9 @@ template <int EPL, int CG>
 static int launch_scan(int grid, int smem, cudaStream_t s, const CUtensorMap& tq, const CUtensorMap& ts,
                        const ScanArgs& a) {
   auto kern = topk_scan_kernel<EPL, CG>;
-  static int configured = 0;  // per instantiation
-  if (smem > configured) {
+  static PerDeviceMax configured;  // per instantiation
+  if (configured.needs(smem)) {
     EVR_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    configured = smem;
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(grid);
@@ -889,10 +888,9 @@ extern "C" int evr_topk_search(const void* store, int64_t N, int D, int64_t row_
   int kp = 1;
   while (kp < k) kp <<= 1;
   const int sel_smem = (kp + p.select_cap) * 8;
-  static int sel_configured = 0;
-  if (sel_smem > 48 * 1024 && sel_smem > sel_configured) {
+  static PerDeviceMax sel_configured;
+  if (sel_smem > 48 * 1024 && sel_configured.needs(sel_smem)) {
     EVR_CHECK_CUDA(cudaFuncSetAttribute(topk_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sel_smem));
-    sel_configured = sel_smem;
   }
   {
     ProfScope ps(PF_FINAL, s);

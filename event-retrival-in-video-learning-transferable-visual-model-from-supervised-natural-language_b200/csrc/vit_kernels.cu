@@ -519,11 +519,10 @@ int launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L,
                      cudaStream_t stream) {
   EVR_REQUIRE(heads * 64 == d, "attention: head dim must be 64 (d=%d heads=%d)", d, heads);
   if (L <= 64 && !causal) {
-    static bool configured_short = false;
-    if (!configured_short) {
+    static PerDeviceMax configured_short;
+    if (configured_short.needs(2 * kAttnStageBytes)) {
       EVR_CHECK_CUDA(cudaFuncSetAttribute(attention_short_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           2 * kAttnStageBytes));
-      configured_short = true;
     }
     const int items = B * heads, slots = sm_count() * 4;        // 4 CTAs (2 x 27 KB stages each) per SM
     const int per_cta = (items + slots - 1) / slots;
@@ -536,11 +535,10 @@ int launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L,
   const int Lp = (L + 63) & ~63;
   const size_t smem = (2 * static_cast<size_t>(Lp) + kAttnLongWarps * 16) * kAttnKStride * 2;  // K, V, per-warp Q/O tiles
   EVR_REQUIRE(smem <= 200 * 1024, "attention: sequence %d too long for the single-CTA K/V staging", L);
-  static size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
+  static PerDeviceMax configured;
+  if (smem > 48 * 1024 && configured.needs(static_cast<int>(smem))) {
     EVR_CHECK_CUDA(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         static_cast<int>(smem)));
-    configured = smem;
   }
   ProfScope ps(PF_ATTN, stream);
   EVR_CHECK_CUDA(launch_pdl(attention_kernel, dim3(heads, B), dim3(kAttnLongWarps * 32), smem, stream, qkv, out, L, d,

@@ -66,3 +66,27 @@ def test_nccl_sharded_search_matches_oracle(tmp_path, N, Q, k):
     for j in range(Q):
         assert so.topk_equal_up_to_ties(i[j, :kk], s[j, :kk], ref_i[j], ref_s[j], 2.0 ** -9)
         assert (i[j, kk:] == -1).all() and np.isneginf(s[j, kk:]).all()   # fewer rows than k: padded tail
+
+
+def test_one_process_two_devices(pkg):
+    """A single process that touches two GPUs: per-device kernel attributes / SM counts must not leak across devices."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs at least 2 CUDA devices")
+    sys.path.insert(0, ROOT)
+    from oracle import search_oracle as so
+    rng = np.random.default_rng(3)
+    raw = rng.standard_normal((20_000, 512)).astype(np.float32)
+    q = rng.standard_normal((150, 512)).astype(np.float32)
+    q /= np.linalg.norm(q, axis=-1, keepdims=True)
+    ref_i, ref_s = so.batched_topk(so.normalise_store(raw), q, 200)
+    sd = pkg.clip.random_visual_state_dict("ViT-B/32", seed=1)
+    frames = torch.randint(0, 256, (5, 224, 224, 3), dtype=torch.uint8)
+    embs = []
+    for dev in (torch.device("cuda:0"), torch.device("cuda:1")):
+        store = pkg.search.FrameStore.from_numpy(raw, device=dev)
+        sc, idx = store.search(torch.from_numpy(q).to(dev), 200)     # k > 128: the large select configuration
+        for j in (0, 77, 149):
+            assert so.topk_equal_up_to_ties(idx[j].cpu().numpy(), sc[j].cpu().numpy(), ref_i[j], ref_s[j], 2.0 ** -9)
+        enc = pkg.vit.VisionEncoder.from_state_dict(sd, "ViT-B/32", device=dev, max_batch=8, prefix="visual.")
+        embs.append(enc.encode(frames.to(dev), normalise=True).cpu())
+    assert torch.equal(embs[0], embs[1])
