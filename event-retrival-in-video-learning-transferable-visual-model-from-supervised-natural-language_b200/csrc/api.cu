@@ -75,6 +75,64 @@ bool pdl_enabled() {
   return on == 1;
 }
 
+bool graphs_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("EVR_NO_GRAPH");
+    on = (e && e[0] == '1') ? 0 : 1;
+  }
+  return on == 1;
+}
+
+int graph_begin(GraphCache& g, int B, cudaStream_t* cap_stream) {
+  (void)B;
+  if (!g.cap && cudaStreamCreateWithFlags(&g.cap, cudaStreamNonBlocking) != cudaSuccess) {
+    cudaGetLastError();
+    return 1;
+  }
+  if (cudaStreamBeginCapture(g.cap, cudaStreamCaptureModeRelaxed) != cudaSuccess) {
+    cudaGetLastError();
+    return 1;
+  }
+  *cap_stream = g.cap;
+  return 0;
+}
+
+int graph_end(GraphCache& g, int B, int body_status, int64_t launches_before) {
+  cudaGraph_t graph = nullptr;
+  const cudaError_t e = cudaStreamEndCapture(g.cap, &graph);
+  const int64_t captured = g_launches.load(std::memory_order_relaxed) - launches_before;
+  g_launches.fetch_sub(captured, std::memory_order_relaxed);  // recorded, not run
+  if (e != cudaSuccess || body_status != 0 || !graph) {
+    cudaGetLastError();
+    if (graph) cudaGraphDestroy(graph);
+    return 1;
+  }
+  const cudaError_t ei = cudaGraphInstantiate(&g.exec[B], graph, 0);
+  cudaGraphDestroy(graph);
+  if (ei != cudaSuccess) {
+    cudaGetLastError();
+    g.exec[B] = nullptr;
+    return 1;
+  }
+  g.kernels[B] = static_cast<int>(captured);
+  g.state[B] = 2;
+  return 0;
+}
+
+int graph_replay(GraphCache& g, int B, cudaStream_t s) {
+  EVR_CHECK_CUDA(cudaGraphLaunch(g.exec[B], s));
+  count_launch(g.kernels[B]);
+  return 0;
+}
+
+void GraphCache::destroy() {
+  for (auto& e : exec)
+    if (e) { cudaGraphExecDestroy(e); e = nullptr; }
+  if (cap) { cudaStreamDestroy(cap); cap = nullptr; }
+  for (auto& st : state) st = 0;
+}
+
 // ---- per-family kernel timing ---------------------------------------------------------------------
 std::atomic<int> g_profile_on{0};
 struct ProfRec {

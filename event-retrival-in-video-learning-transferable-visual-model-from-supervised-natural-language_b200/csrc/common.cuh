@@ -115,4 +115,39 @@ struct ProfScope {
   }
 };
 
+// Small-batch launch path.  Between the first kernel that reads caller memory and the last one that writes it, an
+// encode touches only handle-owned buffers, so for a given batch size the chain (~90 kernels) is a fixed DAG.  At
+// batch <= kMaxBatch the step is bound by the host's launch rate (one query = 0.57 ms of launches for ~0.2 ms of GPU
+// work), so the chain is captured once per batch size -- on a private stream, after one plain pass has done every
+// lazy cudaFuncSetAttribute -- and replayed as one cudaGraphLaunch on the caller's stream.  PDL edges are kept by the
+// capture.  Off while per-family profiling is on, or with EVR_NO_GRAPH=1.
+struct GraphCache {
+  static constexpr int kMaxBatch = 32;
+  cudaStream_t cap = nullptr;
+  cudaGraphExec_t exec[kMaxBatch + 1] = {};
+  int kernels[kMaxBatch + 1] = {};
+  uint8_t state[kMaxBatch + 1] = {};  // 0 never run, 1 ran plain, 2 captured, 3 capture failed (stay plain)
+  void destroy();
+};
+bool graphs_enabled();
+// body(stream) enqueues the chain; returns body's status (0 = ok)
+int graph_begin(GraphCache& g, int B, cudaStream_t* cap_stream);   // 0: capture into *cap_stream; <0: run plain; >0: replay
+int graph_end(GraphCache& g, int B, int body_status, int64_t launches_before);
+int graph_replay(GraphCache& g, int B, cudaStream_t s);
+
+template <typename F>
+inline int run_chain(GraphCache& g, int B, cudaStream_t s, F&& body) {
+  if (B > GraphCache::kMaxBatch || !graphs_enabled() || g_profile_on.load(std::memory_order_relaxed)) return body(s);
+  if (g.state[B] == 0) { g.state[B] = 1; return body(s); }
+  if (g.state[B] == 3) return body(s);
+  if (g.state[B] == 1) {
+    cudaStream_t cs = nullptr;
+    if (graph_begin(g, B, &cs) != 0) { g.state[B] = 3; return body(s); }
+    const int64_t before = g_launches.load(std::memory_order_relaxed);
+    const int st = body(cs);
+    if (graph_end(g, B, st, before) != 0) { g.state[B] = 3; return body(s); }
+  }
+  return graph_replay(g, B, s);
+}
+
 }  // namespace evr

@@ -28,7 +28,8 @@ struct evr_text {
   std::vector<TextLayerW> layers;
   __nv_bfloat16 *hbuf = nullptr, *qkv = nullptr, *attn = nullptr, *fbuf = nullptr, *eot_ln = nullptr;
   float *x = nullptr, *eot = nullptr, *emb = nullptr;
-  int32_t* tokens = nullptr;         // staging for int64 -> int32 converted ids is done on the host side
+  int32_t* tokens = nullptr;         // [max_batch, ctx] copy of the caller's ids for the captured small-batch chain
+  GraphCache graphs;
 };
 
 static int text_copy_f32(float*& cursor, const void* src, size_t n, const float** dst, cudaStream_t s) {
@@ -103,6 +104,8 @@ extern "C" int evr_text_create(const evr_text_cfg* cfg, const void* const* w, in
   EVR_CHECK_CUDA(cudaMalloc(&h->eot, static_cast<size_t>(max_batch) * d * 4));
   EVR_CHECK_CUDA(cudaMalloc(&h->eot_ln, static_cast<size_t>(max_batch) * d * 2));
   EVR_CHECK_CUDA(cudaMalloc(&h->emb, static_cast<size_t>(max_batch) * od * 4));
+  const size_t tok_rows = max_batch < GraphCache::kMaxBatch ? max_batch : GraphCache::kMaxBatch;
+  EVR_CHECK_CUDA(cudaMalloc(&h->tokens, tok_rows * L * sizeof(int32_t)));
   EVR_CHECK_CUDA(cudaStreamSynchronize(s));
   *out = h;
   return 0;
@@ -110,9 +113,10 @@ extern "C" int evr_text_create(const evr_text_cfg* cfg, const void* const* w, in
 
 extern "C" int evr_text_destroy(evr_text* h) {
   if (!h) return 0;
+  h->graphs.destroy();
   cudaFree(h->fparams); cudaFree(h->wparams);
   cudaFree(h->x); cudaFree(h->hbuf); cudaFree(h->qkv); cudaFree(h->attn); cudaFree(h->fbuf);
-  cudaFree(h->eot); cudaFree(h->eot_ln); cudaFree(h->emb);
+  cudaFree(h->eot); cudaFree(h->eot_ln); cudaFree(h->emb); cudaFree(h->tokens);
   delete h;
   return 0;
 }
@@ -125,8 +129,8 @@ static int tgemm(const void* A, int lda, const void* W, int K, int M, int N, con
   return launch_gemm_bf16(A, lda, W, K, a, epi, s);
 }
 
-static int text_chunk(evr_text* h, const int32_t* tokens, int B, void* out, int out_dtype, int l2_normalise,
-                      cudaStream_t s) {
+// embed .. projection GEMM: reads `tokens` and handle buffers, writes h->emb
+static int text_body(evr_text* h, const int32_t* tokens, int B, cudaStream_t s) {
   const int d = h->cfg.width, L = h->cfg.context_length, od = h->cfg.out_dim;
   const int M = B * L;
   if (launch_embed_tokens(tokens, h->tok, h->pos, h->x, B, L, d, h->cfg.vocab_size, s)) return 1;
@@ -143,6 +147,20 @@ static int text_chunk(evr_text* h, const int32_t* tokens, int B, void* out, int 
   if (launch_gather_eot(tokens, h->x, h->eot, B, L, d, s)) return 1;
   if (launch_layernorm(h->eot, d, h->eot_ln, d, 1, h->lnf_g, h->lnf_b, B, d, s)) return 1;
   if (tgemm(h->eot_ln, d, h->w_projT, d, B, od, nullptr, h->emb, od, EPI_F32, s)) return 1;
+  return 0;
+}
+
+static int text_chunk(evr_text* h, const int32_t* tokens, int B, void* out, int out_dtype, int l2_normalise,
+                      cudaStream_t s) {
+  const int L = h->cfg.context_length, od = h->cfg.out_dim;
+  if (B <= GraphCache::kMaxBatch && graphs_enabled()) {
+    // one query is the serving case (embedding_service.py:169): ids are staged so that the chain's pointers are fixed
+    EVR_CHECK_CUDA(cudaMemcpyAsync(h->tokens, tokens, static_cast<size_t>(B) * L * sizeof(int32_t),
+                                   cudaMemcpyDefault, s));
+    if (int r = run_chain(h->graphs, B, s, [&](cudaStream_t cs) { return text_body(h, h->tokens, B, cs); })) return r;
+  } else if (text_body(h, tokens, B, s)) {
+    return 1;
+  }
   if (launch_l2norm_cast(h->emb, out, out_dtype, B, od, l2_normalise, s)) return 1;
   return 0;
 }

@@ -27,6 +27,7 @@ struct evr_vit {
   // workspaces (owned)
   __nv_bfloat16 *a0 = nullptr, *hbuf = nullptr, *qkv = nullptr, *attn = nullptr, *fbuf = nullptr, *cls_ln = nullptr;
   float *x = nullptr, *emb = nullptr;
+  GraphCache graphs;  // captured small-batch chains (common.cuh)
   // L2 residency of the fp32 residual stream (touched 4x per layer, between which ~180 MB of activations stream by)
   size_t l2_persist = 0, l2_window_max = 0;
 };
@@ -154,6 +155,7 @@ extern "C" int evr_vit_create(const evr_vit_cfg* cfg, const void* const* w, int 
 
 extern "C" int evr_vit_destroy(evr_vit* h) {
   if (!h) return 0;
+  h->graphs.destroy();
   cudaFree(h->fparams); cudaFree(h->wparams);
   cudaFree(h->a0); cudaFree(h->x); cudaFree(h->hbuf); cudaFree(h->qkv); cudaFree(h->attn); cudaFree(h->fbuf);
   cudaFree(h->cls_ln); cudaFree(h->emb);
@@ -169,13 +171,11 @@ static int gemm(const void* A, int lda, const void* W, int K, int M, int N, cons
   return launch_gemm_bf16(A, lda, W, K, a, epi, s);
 }
 
-static int encode_chunk(evr_vit* h, const void* pixels, int pix_dtype, int B, void* out, int out_dtype,
-                        int l2_normalise, cudaStream_t s) {
+// patch GEMM .. projection GEMM: reads h->a0, writes h->emb, touches nothing outside the handle
+static int encode_body(evr_vit* h, int B, cudaStream_t s) {
   const int d = h->cfg.width, L = h->L, P = h->g * h->g, od = h->cfg.out_dim;
   const int M = B * L;
-  set_residual_window(h, static_cast<size_t>(M) * d * sizeof(float), s);
   // K1/K2: patch embed (+pos) and class rows
-  if (launch_im2col(pixels, pix_dtype, B, h->cfg.image_size, h->cfg.patch, h->K0p, h->a0, s)) return 1;
   if (gemm(h->a0, h->K0p, h->w_conv, h->K0p, B * P, d, nullptr, h->x, d, EPI_PATCH, s, h->pos, P)) return 1;
   if (launch_cls_rows(h->x, h->cls, h->pos, B, L, d, s)) return 1;
   // ln_pre (fp32 in place: it is the start of the residual stream)
@@ -192,8 +192,21 @@ static int encode_chunk(evr_vit* h, const void* pixels, int pix_dtype, int B, vo
   // ln_post on the class token, projection, optional L2 normalise
   if (launch_layernorm(h->x, static_cast<size_t>(L) * d, h->cls_ln, d, 1, h->ln_post_g, h->ln_post_b, B, d, s)) return 1;
   if (gemm(h->cls_ln, d, h->w_projT, d, B, od, nullptr, h->emb, od, EPI_F32, s)) return 1;
+  return 0;
+}
+
+static int encode_chunk(evr_vit* h, const void* pixels, int pix_dtype, int B, void* out, int out_dtype,
+                        int l2_normalise, cudaStream_t s) {
+  const int d = h->cfg.width, L = h->L, od = h->cfg.out_dim;
+  const int M = B * L;
+  // K1: im2col reads the caller's pixels; everything up to the projection lives in handle buffers (graph-able)
+  if (launch_im2col(pixels, pix_dtype, B, h->cfg.image_size, h->cfg.patch, h->K0p, h->a0, s)) return 1;
+  const bool window = B > GraphCache::kMaxBatch;  // small batches: x is a few MB, no window (and none in the graph)
+  if (window) set_residual_window(h, static_cast<size_t>(M) * d * sizeof(float), s);
+  const int r = run_chain(h->graphs, B, s, [&](cudaStream_t cs) { return encode_body(h, B, cs); });
+  if (r) return r;
   if (launch_l2norm_cast(h->emb, out, out_dtype, B, od, l2_normalise, s)) return 1;
-  set_residual_window(h, 0, s);
+  if (window) set_residual_window(h, 0, s);
   return 0;
 }
 

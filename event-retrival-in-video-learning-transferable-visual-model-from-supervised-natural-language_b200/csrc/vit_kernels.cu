@@ -230,11 +230,17 @@ __device__ __forceinline__ void ldmatrix_x4_trans(uint32_t (&r)[4], const void* 
                : "r"(static_cast<uint32_t>(__cvta_generic_to_shared(smem_src))));
 }
 
+// LC: compile-time sequence length (50 = ViT-B/32 at 224 px: the guards below fold away), 0 = use the runtime L.
+template <int LC>
 __global__ void __launch_bounds__(128)
-attention_short_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, int L, int d, int heads,
+attention_short_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, int L_rt, int d, int heads,
                        int items, float scale_log2e) {
   pdl_launch_dependents();
   pdl_wait();
+  const int L = LC ? LC : L_rt;
+  // key groups (8 keys) that hold a key / that are entirely valid: groups past nt_end cost nothing, only
+  // [nt_full, nt_end) is masked.  ncu showed the loop bound by issue slots spent on ALU work, not by the tensor pipe.
+  const int nt_end = (L + 7) >> 3, nt_full = L >> 3;
   extern __shared__ __align__(16) uint8_t attn_smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const int ld = 3 * d;
@@ -287,22 +293,27 @@ attention_short_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __r
       for (int nt = 0; nt < 8; nt += 2) {
         s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
         s[nt + 1][0] = s[nt + 1][1] = s[nt + 1][2] = s[nt + 1][3] = 0.f;
+        if (nt < nt_end) {
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk) {
-          uint32_t kb[4];  // K[key 8nt + g][dims 16kk + {0,8} + 2t..] for key tiles nt, nt+1
-          ldmatrix_x4(kb, Ks + ((nt + (lane >> 4)) * 8 + (lane & 7)) * kAttnKStride + 16 * kk + ((lane >> 3) & 1) * 8);
-          mma_bf16_16816(s[nt], qa[kk], kb[0], kb[1]);
-          mma_bf16_16816(s[nt + 1], qa[kk], kb[2], kb[3]);
+          for (int kk = 0; kk < 4; ++kk) {
+            uint32_t kb[4];  // K[key 8nt + g][dims 16kk + {0,8} + 2t..] for key tiles nt, nt+1
+            ldmatrix_x4(kb, Ks + ((nt + (lane >> 4)) * 8 + (lane & 7)) * kAttnKStride + 16 * kk + ((lane >> 3) & 1) * 8);
+            mma_bf16_16816(s[nt], qa[kk], kb[0], kb[1]);
+            if (nt + 1 < nt_end) mma_bf16_16816(s[nt + 1], qa[kk], kb[2], kb[3]);
+          }
         }
       }
+      // raw scores: the positive scale commutes with the maximum and is folded into the exponent's FFMA below
       float mx0 = -INFINITY, mx1 = -INFINITY;
 #pragma unroll
       for (int nt = 0; nt < 8; ++nt) {
-        const int col = nt * 8 + 2 * t;
-        s[nt][0] = col < L ? s[nt][0] * scale_log2e : -INFINITY;
-        s[nt][1] = col + 1 < L ? s[nt][1] * scale_log2e : -INFINITY;
-        s[nt][2] = col < L ? s[nt][2] * scale_log2e : -INFINITY;
-        s[nt][3] = col + 1 < L ? s[nt][3] * scale_log2e : -INFINITY;
+        if (nt >= nt_full) {
+          const int col = nt * 8 + 2 * t;
+          s[nt][0] = col < L ? s[nt][0] : -INFINITY;
+          s[nt][1] = col + 1 < L ? s[nt][1] : -INFINITY;
+          s[nt][2] = col < L ? s[nt][2] : -INFINITY;
+          s[nt][3] = col + 1 < L ? s[nt][3] : -INFINITY;
+        }
         mx0 = fmaxf(mx0, fmaxf(s[nt][0], s[nt][1]));
         mx1 = fmaxf(mx1, fmaxf(s[nt][2], s[nt][3]));
       }
@@ -311,20 +322,26 @@ attention_short_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __r
       mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
       mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
       float l0 = 0.f, l1 = 0.f;
+      const float ms0 = -mx0 * scale_log2e, ms1 = -mx1 * scale_log2e;
 #pragma unroll
       for (int nt = 0; nt < 8; ++nt) {
-        s[nt][0] = fast_exp2(s[nt][0] - mx0);
-        s[nt][1] = fast_exp2(s[nt][1] - mx0);
-        s[nt][2] = fast_exp2(s[nt][2] - mx1);
-        s[nt][3] = fast_exp2(s[nt][3] - mx1);
-        l0 += s[nt][0] + s[nt][1];
-        l1 += s[nt][2] + s[nt][3];
+        if (nt < nt_end) {
+          s[nt][0] = fast_exp2(fmaf(s[nt][0], scale_log2e, ms0));
+          s[nt][1] = fast_exp2(fmaf(s[nt][1], scale_log2e, ms0));
+          s[nt][2] = fast_exp2(fmaf(s[nt][2], scale_log2e, ms1));
+          s[nt][3] = fast_exp2(fmaf(s[nt][3], scale_log2e, ms1));
+          l0 += s[nt][0] + s[nt][1];
+          l1 += s[nt][2] + s[nt][3];
+        } else {
+          s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+        }
       }
       float o[8][4];
 #pragma unroll
       for (int nt = 0; nt < 8; ++nt) { o[nt][0] = o[nt][1] = o[nt][2] = o[nt][3] = 0.f; }
 #pragma unroll
       for (int kk = 0; kk < 4; ++kk) {
+        if (2 * kk >= nt_end) break;  // 16-key groups past the last key carry p = 0
         uint32_t pa[4];
         pa[0] = pack2_bf16(s[2 * kk][0], s[2 * kk][1]);
         pa[1] = pack2_bf16(s[2 * kk][2], s[2 * kk][3]);
@@ -362,6 +379,85 @@ attention_short_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __r
       }
     }
     __syncthreads();  // this stage is refilled by the prefetch issued at the top of the next iteration
+  }
+}
+
+// One 64-key block of the flash loop for a warp's 16-query tile.  Scores stay in raw (unscaled) units: the row maximum
+// commutes with the positive scale, which is folded into the exponent's FFMA (p = 2^(s*c - m*c)); the running output
+// is rescaled only when some row's maximum moved (warp vote).  ncu on L = 257 showed the loop issue-bound on ALU work
+// (tensor pipe 37 %, issue slots 52 %, ~350 non-MMA instructions per 64 MMAs), hence the lean full-block path.
+// PARTIAL: the block holds masked keys (sequence tail, causal diagonal): groups >= nt_end are skipped entirely.
+template <bool PARTIAL>
+__device__ __forceinline__ void attn_block(const __nv_bfloat16* Ks, const __nv_bfloat16* Vs, int kb, int lane, int t,
+                                           const uint32_t (&qa)[4][4], float (&o)[8][4], float& mx0, float& mx1,
+                                           float& l0, float& l1, float c, int lim0, int lim1, int nt_end) {
+  float s[8][4];
+#pragma unroll
+  for (int nt = 0; nt < 8; nt += 2) {
+    s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+    s[nt + 1][0] = s[nt + 1][1] = s[nt + 1][2] = s[nt + 1][3] = 0.f;
+    if (!PARTIAL || nt < nt_end) {
+#pragma unroll
+      for (int kk = 0; kk < 4; ++kk) {
+        uint32_t kf[4];
+        ldmatrix_x4(kf, Ks + (kb * 64 + (nt + (lane >> 4)) * 8 + (lane & 7)) * kAttnKStride + 16 * kk +
+                            ((lane >> 3) & 1) * 8);
+        mma_bf16_16816(s[nt], qa[kk], kf[0], kf[1]);
+        mma_bf16_16816(s[nt + 1], qa[kk], kf[2], kf[3]);
+      }
+    }
+  }
+  float bm0 = -INFINITY, bm1 = -INFINITY;
+#pragma unroll
+  for (int nt = 0; nt < 8; ++nt) {
+    if (PARTIAL) {
+      const int col = kb * 64 + nt * 8 + 2 * t;
+      s[nt][0] = col < lim0 ? s[nt][0] : -INFINITY;
+      s[nt][1] = col + 1 < lim0 ? s[nt][1] : -INFINITY;
+      s[nt][2] = col < lim1 ? s[nt][2] : -INFINITY;
+      s[nt][3] = col + 1 < lim1 ? s[nt][3] : -INFINITY;
+    }
+    bm0 = fmaxf(bm0, fmaxf(s[nt][0], s[nt][1]));
+    bm1 = fmaxf(bm1, fmaxf(s[nt][2], s[nt][3]));
+  }
+  bm0 = fmaxf(bm0, __shfl_xor_sync(0xffffffffu, bm0, 1));
+  bm0 = fmaxf(bm0, __shfl_xor_sync(0xffffffffu, bm0, 2));
+  bm1 = fmaxf(bm1, __shfl_xor_sync(0xffffffffu, bm1, 1));
+  bm1 = fmaxf(bm1, __shfl_xor_sync(0xffffffffu, bm1, 2));
+  const float mn0 = fmaxf(mx0, bm0), mn1 = fmaxf(mx1, bm1);  // finite: key block 0 always holds key 0
+  if (__any_sync(0xffffffffu, mn0 > mx0 || mn1 > mx1)) {
+    const float a0 = fast_exp2((mx0 - mn0) * c), a1 = fast_exp2((mx1 - mn1) * c);
+    l0 *= a0; l1 *= a1;
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) { o[nt][0] *= a0; o[nt][1] *= a0; o[nt][2] *= a1; o[nt][3] *= a1; }
+    mx0 = mn0; mx1 = mn1;
+  }
+  const float ms0 = -mn0 * c, ms1 = -mn1 * c;
+#pragma unroll
+  for (int nt = 0; nt < 8; ++nt) {
+    s[nt][0] = fast_exp2(fmaf(s[nt][0], c, ms0));
+    s[nt][1] = fast_exp2(fmaf(s[nt][1], c, ms0));
+    s[nt][2] = fast_exp2(fmaf(s[nt][2], c, ms1));
+    s[nt][3] = fast_exp2(fmaf(s[nt][3], c, ms1));
+    l0 += s[nt][0] + s[nt][1];
+    l1 += s[nt][2] + s[nt][3];
+  }
+#pragma unroll
+  for (int kk = 0; kk < 4; ++kk) {
+    if (PARTIAL && 2 * kk >= nt_end) break;  // 16-key groups past the last visible key carry p = 0
+    uint32_t pa[4];
+    pa[0] = pack2_bf16(s[2 * kk][0], s[2 * kk][1]);
+    pa[1] = pack2_bf16(s[2 * kk][2], s[2 * kk][3]);
+    pa[2] = pack2_bf16(s[2 * kk + 1][0], s[2 * kk + 1][1]);
+    pa[3] = pack2_bf16(s[2 * kk + 1][2], s[2 * kk + 1][3]);
+#pragma unroll
+    for (int nt = 0; nt < 8; nt += 2) {
+      uint32_t vb[4];
+      ldmatrix_x4_trans(vb, Vs + (kb * 64 + 16 * kk + ((lane >> 3) & 1) * 8 + (lane & 7)) * kAttnKStride +
+                                (nt + (lane >> 4)) * 8);
+      mma_bf16_16816(o[nt], pa, vb[0], vb[1]);
+      mma_bf16_16816(o[nt + 1], pa, vb[2], vb[3]);
+    }
   }
 }
 
@@ -407,7 +503,10 @@ attention_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restric
   }
   __syncthreads();
 
-  const int num_mt = (L + 15) >> 4;
+  // L = 16 n + 1 (257 tokens, ViT-L/14): the 17th query tile would hold one row and cost one warp a third full round
+  // while the other seven idle; that row is computed by the whole CTA on the FMA pipes after the tile loop instead.
+  const bool lone_row = !causal && (L & 15) == 1 && L > 16;
+  const int num_mt = lone_row ? (L >> 4) : ((L + 15) >> 4);
   for (int mt = warp; mt < num_mt; mt += kAttnLongWarps) {
     const int m0 = mt * 16;
     // ---- Q tile -> staging -> A fragments
@@ -431,66 +530,14 @@ attention_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restric
     float mx0 = -INFINITY, mx1 = -INFINITY, l0 = 0.f, l1 = 0.f;
     const int kb_end = causal ? min(Lp / 64, (m0 + 15) / 64 + 1) : Lp / 64;
     for (int kb = 0; kb < kb_end; ++kb) {
-      float s[8][4];
-#pragma unroll
-      for (int nt = 0; nt < 8; nt += 2) {
-        s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
-        s[nt + 1][0] = s[nt + 1][1] = s[nt + 1][2] = s[nt + 1][3] = 0.f;
-#pragma unroll
-        for (int kk = 0; kk < 4; ++kk) {
-          uint32_t kf[4];
-          ldmatrix_x4(kf, Ks + (kb * 64 + (nt + (lane >> 4)) * 8 + (lane & 7)) * kAttnKStride + 16 * kk +
-                              ((lane >> 3) & 1) * 8);
-          mma_bf16_16816(s[nt], qa[kk], kf[0], kf[1]);
-          mma_bf16_16816(s[nt + 1], qa[kk], kf[2], kf[3]);
-        }
-      }
-      float bm0 = -INFINITY, bm1 = -INFINITY;
-#pragma unroll
-      for (int nt = 0; nt < 8; ++nt) {
-        const int col = kb * 64 + nt * 8 + 2 * t;
-        s[nt][0] = col < lim0 ? s[nt][0] * scale_log2e : -INFINITY;
-        s[nt][1] = col + 1 < lim0 ? s[nt][1] * scale_log2e : -INFINITY;
-        s[nt][2] = col < lim1 ? s[nt][2] * scale_log2e : -INFINITY;
-        s[nt][3] = col + 1 < lim1 ? s[nt][3] * scale_log2e : -INFINITY;
-        bm0 = fmaxf(bm0, fmaxf(s[nt][0], s[nt][1]));
-        bm1 = fmaxf(bm1, fmaxf(s[nt][2], s[nt][3]));
-      }
-      bm0 = fmaxf(bm0, __shfl_xor_sync(0xffffffffu, bm0, 1));
-      bm0 = fmaxf(bm0, __shfl_xor_sync(0xffffffffu, bm0, 2));
-      bm1 = fmaxf(bm1, __shfl_xor_sync(0xffffffffu, bm1, 1));
-      bm1 = fmaxf(bm1, __shfl_xor_sync(0xffffffffu, bm1, 2));
-      const float mn0 = fmaxf(mx0, bm0), mn1 = fmaxf(mx1, bm1);  // finite: key block 0 always holds key 0
-      const float a0 = fast_exp2(mx0 - mn0), a1 = fast_exp2(mx1 - mn1);
-      l0 *= a0; l1 *= a1;
-#pragma unroll
-      for (int nt = 0; nt < 8; ++nt) { o[nt][0] *= a0; o[nt][1] *= a0; o[nt][2] *= a1; o[nt][3] *= a1; }
-#pragma unroll
-      for (int nt = 0; nt < 8; ++nt) {
-        s[nt][0] = fast_exp2(s[nt][0] - mn0);
-        s[nt][1] = fast_exp2(s[nt][1] - mn0);
-        s[nt][2] = fast_exp2(s[nt][2] - mn1);
-        s[nt][3] = fast_exp2(s[nt][3] - mn1);
-        l0 += s[nt][0] + s[nt][1];
-        l1 += s[nt][2] + s[nt][3];
-      }
-      mx0 = mn0; mx1 = mn1;
-#pragma unroll
-      for (int kk = 0; kk < 4; ++kk) {
-        uint32_t pa[4];
-        pa[0] = pack2_bf16(s[2 * kk][0], s[2 * kk][1]);
-        pa[1] = pack2_bf16(s[2 * kk][2], s[2 * kk][3]);
-        pa[2] = pack2_bf16(s[2 * kk + 1][0], s[2 * kk + 1][1]);
-        pa[3] = pack2_bf16(s[2 * kk + 1][2], s[2 * kk + 1][3]);
-#pragma unroll
-        for (int nt = 0; nt < 8; nt += 2) {
-          uint32_t vb[4];
-          ldmatrix_x4_trans(vb, Vs + (kb * 64 + 16 * kk + ((lane >> 3) & 1) * 8 + (lane & 7)) * kAttnKStride +
-                                    (nt + (lane >> 4)) * 8);
-          mma_bf16_16816(o[nt], pa, vb[0], vb[1]);
-          mma_bf16_16816(o[nt + 1], pa, vb[2], vb[3]);
-        }
-      }
+      // 8-key groups of this block with a key visible to the tile (warp-uniform): the last block of L = 257 holds one
+      // key, of L = 197 five.  Full blocks take the lean path: no masking, no guards.
+      const int vis = (causal ? min(L, m0 + 16) : L) - kb * 64;
+      const bool partial = vis < 64 || (causal && kb * 64 + 63 > m0);
+      if (partial)
+        attn_block<true>(Ks, Vs, kb, lane, t, qa, o, mx0, mx1, l0, l1, scale_log2e, lim0, lim1, min(8, (vis + 7) >> 3));
+      else
+        attn_block<false>(Ks, Vs, kb, lane, t, qa, o, mx0, mx1, l0, l1, scale_log2e, lim0, lim1, 8);
     }
     l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
     l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
@@ -513,6 +560,67 @@ attention_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restric
     }
     __syncwarp();  // the staging tile is rewritten by the next query tile
   }
+  if (lone_row) {
+    // ---- last query row, all 256 threads.  Scratch: the per-warp Q/O tiles (free after the barrier).
+    __syncthreads();
+    float* sc = reinterpret_cast<float*>(Vs + Lp * kAttnKStride);  // [Lp] scores -> probabilities
+    float* red = sc + Lp;                                          // [8] warp maxima, [8] warp sums
+    float* part = red + 16;                                        // [8][64] partial outputs
+    const int r = L - 1;
+    uint4 q4[8];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) q4[c] = *reinterpret_cast<const uint4*>(qkv + (row0 + r) * ld + h * 64 + c * 8);
+    float tmax = -INFINITY;
+    for (int j = threadIdx.x; j < L; j += kAttnLongWarps * 32) {
+      float acc = 0.f;
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        const uint4 k4 = *reinterpret_cast<const uint4*>(Ks + j * kAttnKStride + c * 8);
+        const __nv_bfloat162* qp = reinterpret_cast<const __nv_bfloat162*>(&q4[c]);
+        const __nv_bfloat162* kp = reinterpret_cast<const __nv_bfloat162*>(&k4);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 a = __bfloat1622float2(qp[e]), bq = __bfloat1622float2(kp[e]);
+          acc = fmaf(a.x, bq.x, acc);
+          acc = fmaf(a.y, bq.y, acc);
+        }
+      }
+      acc *= scale_log2e;
+      sc[j] = acc;
+      tmax = fmaxf(tmax, acc);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) tmax = fmaxf(tmax, __shfl_xor_sync(0xffffffffu, tmax, o));
+    if (lane == 0) red[warp] = tmax;
+    __syncthreads();
+    float rmax = red[0];
+#pragma unroll
+    for (int w = 1; w < kAttnLongWarps; ++w) rmax = fmaxf(rmax, red[w]);
+    // warp w owns keys w, w + 8, ...; lane owns output dims 2 lane, 2 lane + 1
+    float ox = 0.f, oy = 0.f, lsum = 0.f;
+    for (int j = warp; j < L; j += kAttnLongWarps) {
+      const float pj = fast_exp2(sc[j] - rmax);
+      const float2 v2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(Vs + j * kAttnKStride + 2 * lane));
+      ox = fmaf(pj, v2.x, ox);
+      oy = fmaf(pj, v2.y, oy);
+      lsum += pj;
+    }
+    part[warp * 64 + 2 * lane] = ox;
+    part[warp * 64 + 2 * lane + 1] = oy;
+    if (lane == 0) red[8 + warp] = lsum;
+    __syncthreads();
+    if (warp == 0) {
+      float tx = 0.f, ty = 0.f, lt = 0.f;
+#pragma unroll
+      for (int w = 0; w < kAttnLongWarps; ++w) {
+        tx += part[w * 64 + 2 * lane];
+        ty += part[w * 64 + 2 * lane + 1];
+        lt += red[8 + w];
+      }
+      const float inv = 1.0f / lt;
+      *reinterpret_cast<uint32_t*>(out + (row0 + r) * d + h * 64 + 2 * lane) = pack2_bf16(tx * inv, ty * inv);
+    }
+  }
 }
 
 int launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int d, int heads, int causal,
@@ -521,14 +629,18 @@ int launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L,
   if (L <= 64 && !causal) {
     static PerDeviceMax configured_short;
     if (configured_short.needs(2 * kAttnStageBytes)) {
-      EVR_CHECK_CUDA(cudaFuncSetAttribute(attention_short_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+      EVR_CHECK_CUDA(cudaFuncSetAttribute(attention_short_kernel<50>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          2 * kAttnStageBytes));
+      EVR_CHECK_CUDA(cudaFuncSetAttribute(attention_short_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           2 * kAttnStageBytes));
     }
     const int items = B * heads, slots = sm_count() * 4;        // 4 CTAs (2 x 27 KB stages each) per SM
     const int per_cta = (items + slots - 1) / slots;
     const int grid = (items + per_cta - 1) / per_cta;           // every CTA walks the same number of items (+-1)
     ProfScope ps(PF_ATTN, stream);
-    EVR_CHECK_CUDA(launch_pdl(attention_short_kernel, dim3(grid), dim3(128), 2 * kAttnStageBytes, stream, qkv, out, L, d, heads, items, 0.125f * 1.4426950408889634f));
+    EVR_CHECK_CUDA(launch_pdl(L == 50 ? attention_short_kernel<50> : attention_short_kernel<0>, dim3(grid), dim3(128),
+                              2 * kAttnStageBytes, stream, qkv, out, L, d, heads, items,
+                              0.125f * 1.4426950408889634f));
     EVR_CHECK_LAUNCH();
     return 0;
   }

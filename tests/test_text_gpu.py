@@ -116,3 +116,17 @@ def test_clip_model_text_and_service_query_path(pkg, cuda, tower, tmp_path, monk
     got_i = np.array([int(f.split(".")[0]) for f in got])
     assert so.topk_equal_up_to_ties(got_i, np.array([s for _, s in pairs]), ref_i[0], ref_s[0], 2.0 ** -9)
     assert abs(svc.extract_query_confidence(got[0], query) - pairs[0][1]) < 1e-5
+
+
+def test_single_query_graph_replay_is_identical(pkg, cuda, tower):
+    """One query (the serving case) runs as a captured graph from its third call: same bits, new ids honoured."""
+    enc = pkg.text.TextEncoder.from_state_dict(tower.state_dict(), device=cuda, max_batch=8)
+    tokens = to.synthetic_tokens(6, seed=11).to(cuda)
+    plain = [enc.encode(tokens[i:i + 1]).clone() for i in range(3)]          # call 1 plain, 2 capture, 3 replay
+    again = [enc.encode(tokens[i:i + 1]).clone() for i in range(3)]          # all replays
+    for p, a in zip(plain, again):
+        assert torch.equal(p, a)
+    whole = enc.encode(tokens)
+    assert torch.equal(whole[:3], torch.cat(again))
+    ref = to.encode_text(tower, tokens.cpu(), normalise=False)
+    assert _cos(whole.cpu().numpy(), ref).min() >= MIN_COS

@@ -181,3 +181,31 @@ def test_retrieval_metrics_unchanged(pkg, cuda, name, n_img):
         if kk <= k:
             r_at_k = float(np.mean((idx[:, :kk] == gt[:, None]).any(1)))
             assert abs(r_at_k - m_ref["t2i"][f"R@{kk}"]) <= max(2.0 / (n_img * caps), 0.01) + 1e-9, (kk, r_at_k, m_ref["t2i"])
+
+
+def test_small_batch_graph_replay_is_identical(pkg, cuda, b32):
+    """Batches <= 32 run as a captured CUDA graph from their third call on (plain, capture, replay...): same bits as
+    the plain pass, fresh inputs are honoured, and the launch counter advances by the same number of kernels."""
+    visual, u8, pix, ref = b32
+    enc = pkg.vit.VisionEncoder.from_state_dict(visual.state_dict(), "ViT-B/32", device=cuda, max_batch=64)
+    a, b = pix[:5].to(cuda), pix[5:10].to(cuda)
+    lib = pkg._lib.lib
+    c0 = lib.evr_launch_count()
+    plain = enc.encode(a).clone()
+    c1 = lib.evr_launch_count()
+    captured = enc.encode(a).clone()       # capture + first replay
+    c2 = lib.evr_launch_count()
+    replay_b = enc.encode(b).clone()       # replay on other pixels
+    replay_a = enc.encode(a).clone()
+    c3 = lib.evr_launch_count()
+    assert torch.equal(plain, captured) and torch.equal(plain, replay_a)
+    assert not torch.equal(replay_a, replay_b)
+    assert _cos(replay_b.cpu().numpy(), ref[5:10]).min() >= MIN_COS
+    assert c1 - c0 == c2 - c1 and c3 - c2 == 2 * (c1 - c0)
+    # a side stream works too (the graph is launched on the caller's stream)
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        on_side = enc.encode(b).clone()
+    s.synchronize()
+    assert torch.equal(on_side, replay_b)
