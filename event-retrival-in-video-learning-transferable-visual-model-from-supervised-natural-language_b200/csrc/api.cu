@@ -75,15 +75,6 @@ bool pdl_enabled() {
   return on == 1;
 }
 
-bool ln_fuse_enabled() {
-  static int on = -1;
-  if (on < 0) {
-    const char* e = getenv("EVR_NO_LNFUSE");
-    on = (e && e[0] == '1') ? 0 : 1;
-  }
-  return on == 1;
-}
-
 bool graphs_enabled() {
   static int on = -1;
   if (on < 0) {

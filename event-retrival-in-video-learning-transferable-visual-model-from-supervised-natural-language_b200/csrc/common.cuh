@@ -69,9 +69,6 @@ struct PerDeviceMax {
 // writes.  Every kernel launched this way calls pdl_wait() before its first access to activations (which also keeps
 // completion transitive along the chain).  EVR_NO_PDL=1 turns the attribute off.
 bool pdl_enabled();
-// LayerNorm fused into the preceding residual GEMM (gemm_tc.cuh, "last arriver"); EVR_NO_LNFUSE=1 keeps the
-// stand-alone layernorm_kernel launches (same bits, used for A/B runs and by the parity test).
-bool ln_fuse_enabled();
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
                               Args&&... args) {

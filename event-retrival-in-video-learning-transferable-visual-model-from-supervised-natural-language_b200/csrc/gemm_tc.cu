@@ -74,11 +74,6 @@ int launch_gemm_bf16(const void* A, int lda, const void* W, int ldw, const GemmA
   EVR_REQUIRE(args.K % kGemmBlockK == 0, "GEMM: K=%d must be a multiple of %d", args.K, kGemmBlockK);
   EVR_REQUIRE(args.N % 32 == 0, "GEMM: N=%d must be a multiple of 32", args.N);
   EVR_REQUIRE(args.ldo % 8 == 0, "GEMM: ldo=%d must be a multiple of 8", args.ldo);
-  if (args.ln_out != nullptr) {
-    EVR_REQUIRE(epilogue == EPI_F32_RESID && args.ldo == args.N && args.ln_gamma && args.ln_beta && args.ln_counters &&
-                    (args.N == 512 || args.N == 768 || args.N == 1024),
-                "GEMM: fused LayerNorm needs the residual epilogue over whole rows of width 512 | 768 | 1024");
-  }
   const int sms = sm_count();
   // CTA pairs (256-row tiles) whenever there is more than one 128-row tile of work
   const int cg = (args.M > kGemmBlockM && sms % 2 == 0) ? 2 : 1;

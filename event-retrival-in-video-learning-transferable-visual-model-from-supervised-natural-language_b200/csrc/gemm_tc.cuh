@@ -32,14 +32,6 @@ struct GemmArgs {
   int ldo;
   const float* pos;   // EPI_PATCH: positional_embedding [(P+1), N]
   int patches;        // EPI_PATCH: P
-  // EPI_F32_RESID, optional: the LayerNorm that follows the residual add (ln_2 after out_proj, the next block's ln_1
-  // after c_proj), fused.  A 128-row block of x is final once all N tiles over it have issued their reductions; every
-  // CTA counts its tile in on ln_counters[row block] and the LAST ARRIVER normalises those 128 rows (N = row width)
-  // into ln_out with its epilogue warps while the MMA warp is already on the next tile.
-  const float* ln_gamma;   // [N]
-  const float* ln_beta;    // [N]
-  __nv_bfloat16* ln_out;   // [M, N] bf16, row stride N; nullptr = no fused LayerNorm
-  int* ln_counters;        // [ceil(M / 128)], zero on entry; left zero on exit
 };
 
 constexpr int kGemmBlockM = 128;
@@ -97,58 +89,6 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&t);
 }
 
-// LayerNorm of rows [row_begin, row_end) of x (fp32, row stride d = 128 D4) into bf16, by the 8 epilogue warps of one
-// CTA: the arithmetic (order included) of layernorm_kernel in vit_kernels.cu, so fused and stand-alone agree bit for bit.
-// Two rows per warp in flight; x is read with ld.global.cg: the rows were just written by L2 reductions.
-template <int D4>
-__device__ __forceinline__ void ln_rows_from_l2(const float* x, __nv_bfloat16* out, const float* __restrict__ gamma,
-                                                const float* __restrict__ beta, int row_begin, int row_end, int ew,
-                                                int lane) {
-  constexpr int d = D4 * 128;
-  const float4* g4 = reinterpret_cast<const float4*>(gamma);
-  const float4* b4 = reinterpret_cast<const float4*>(beta);
-  for (int r = row_begin + 2 * ew; r < row_end; r += 16) {
-    float4 v[2][D4];
-#pragma unroll
-    for (int j = 0; j < 2; ++j) {
-      const int row = min(r + j, row_end - 1);
-      const float4* x4 = reinterpret_cast<const float4*>(x + static_cast<size_t>(row) * d);
-#pragma unroll
-      for (int i = 0; i < D4; ++i) v[j][i] = __ldcg(x4 + lane + 32 * i);
-    }
-#pragma unroll
-    for (int j = 0; j < 2; ++j) {
-      if (r + j >= row_end) break;
-      float sum = 0.f;
-#pragma unroll
-      for (int i = 0; i < D4; ++i) sum += (v[j][i].x + v[j][i].y) + (v[j][i].z + v[j][i].w);
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-      const float mean = sum * (1.0f / d);
-      float sq = 0.f;
-#pragma unroll
-      for (int i = 0; i < D4; ++i) {
-        float4& w = v[j][i];
-        w.x -= mean; w.y -= mean; w.z -= mean; w.w -= mean;
-        sq += (w.x * w.x + w.y * w.y) + (w.z * w.z + w.w * w.w);
-      }
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
-      const float rstd = rsqrtf(sq * (1.0f / d) + 1e-5f);
-      uint2* o2 = reinterpret_cast<uint2*>(out + static_cast<size_t>(r + j) * d);
-#pragma unroll
-      for (int i = 0; i < D4; ++i) {
-        const float4 gm = __ldg(g4 + lane + 32 * i), bt = __ldg(b4 + lane + 32 * i);
-        const float4 w = v[j][i];
-        uint2 pk;
-        pk.x = pack_bf16x2(w.x * rstd * gm.x + bt.x, w.y * rstd * gm.y + bt.y);
-        pk.y = pack_bf16x2(w.z * rstd * gm.z + bt.z, w.w * rstd * gm.w + bt.w);
-        o2[lane + 32 * i] = pk;
-      }
-    }
-  }
-}
-
 template <int BLOCK_N, int EPI, int CG>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
@@ -165,7 +105,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   uint64_t* tmem_full = bars + 2 * kStages;      // [2]        MMA -> epilogue
   uint64_t* tmem_empty = bars + 2 * kStages + 2; // [2]        epilogue -> MMA
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
-  int* ln_flag = reinterpret_cast<int*>(bars + 2 * kStages + 5);  // fused LayerNorm: "this CTA arrived last"
 
   pdl_launch_dependents();
   const int warp = threadIdx.x >> 5;
@@ -383,30 +322,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             }
           }
           __syncwarp();  // the staging tile is rewritten by the next chunk
-        }
-      }
-      if constexpr (EPI == EPI_F32_RESID) {
-        if (args.ln_out != nullptr) {  // kernel-uniform
-          // count this tile in on its 128-row block (release: fence after this thread's reductions, CTA barrier over
-          // the epilogue warps, one atomic); the last of the num_n arrivals owns the block (acquire: fence, barrier)
-          __threadfence();
-          asm volatile("bar.sync 1, 256;" ::: "memory");
-          if (ew == 0 && lane == 0) {
-            int* ctr = args.ln_counters + m_idx * CG + static_cast<int>(rank);
-            const int last = atomicAdd(ctr, 1) == num_n - 1;
-            if (last) *ctr = 0;  // re-armed for the next launch
-            __threadfence();
-            *ln_flag = last;
-          }
-          asm volatile("bar.sync 1, 256;" ::: "memory");
-          if (*ln_flag) {
-            const int rb = m_idx * kTileM + static_cast<int>(rank) * kGemmBlockM;
-            const int re = min(rb + kGemmBlockM, args.M);
-            const float* x = static_cast<const float*>(args.out);
-            if (args.N == 768) ln_rows_from_l2<6>(x, args.ln_out, args.ln_gamma, args.ln_beta, rb, re, ew, lane);
-            else if (args.N == 1024) ln_rows_from_l2<8>(x, args.ln_out, args.ln_gamma, args.ln_beta, rb, re, ew, lane);
-            else ln_rows_from_l2<4>(x, args.ln_out, args.ln_gamma, args.ln_beta, rb, re, ew, lane);
-          }
         }
       }
       as ^= 1;

@@ -28,7 +28,6 @@ struct evr_vit {
   __nv_bfloat16 *a0 = nullptr, *hbuf = nullptr, *qkv = nullptr, *attn = nullptr, *fbuf = nullptr, *cls_ln = nullptr;
   float *x = nullptr, *emb = nullptr;
   GraphCache graphs;  // captured small-batch chains (common.cuh)
-  int* ln_counters = nullptr;  // arrival counters of the fused LayerNorm, one per 128 rows (gemm_tc.cuh)
   // L2 residency of the fp32 residual stream (touched 4x per layer, between which ~180 MB of activations stream by)
   size_t l2_persist = 0, l2_window_max = 0;
 };
@@ -135,8 +134,6 @@ extern "C" int evr_vit_create(const evr_vit_cfg* cfg, const void* const* w, int 
   EVR_CHECK_CUDA(cudaMalloc(&h->fbuf, rows * 4 * d * 2));
   EVR_CHECK_CUDA(cudaMalloc(&h->cls_ln, static_cast<size_t>(max_batch) * d * 2));
   EVR_CHECK_CUDA(cudaMalloc(&h->emb, static_cast<size_t>(max_batch) * od * 4));
-  EVR_CHECK_CUDA(cudaMalloc(&h->ln_counters, (rows / 128 + 4) * sizeof(int)));
-  EVR_CHECK_CUDA(cudaMemsetAsync(h->ln_counters, 0, (rows / 128 + 4) * sizeof(int), s));
   {
     int dev = 0, max_persist = 0, max_window = 0;
     cudaGetDevice(&dev);
@@ -161,7 +158,7 @@ extern "C" int evr_vit_destroy(evr_vit* h) {
   h->graphs.destroy();
   cudaFree(h->fparams); cudaFree(h->wparams);
   cudaFree(h->a0); cudaFree(h->x); cudaFree(h->hbuf); cudaFree(h->qkv); cudaFree(h->attn); cudaFree(h->fbuf);
-  cudaFree(h->cls_ln); cudaFree(h->emb); cudaFree(h->ln_counters);
+  cudaFree(h->cls_ln); cudaFree(h->emb);
   delete h;
   return 0;
 }
@@ -174,17 +171,6 @@ static int gemm(const void* A, int lda, const void* W, int K, int M, int N, cons
   return launch_gemm_bf16(A, lda, W, K, a, epi, s);
 }
 
-// x += A W^T + bias, then (fused) ln_out = LayerNorm(x; g, b) for the rows as they become final
-static int gemm_resid_ln(evr_vit* h, const void* A, int lda, const void* W, int K, int M, const float* bias,
-                         const float* g, const float* b, cudaStream_t s) {
-  const int d = h->cfg.width;
-  GemmArgs a{};
-  a.M = M; a.N = d; a.K = K;
-  a.bias = bias; a.out = h->x; a.ldo = d;
-  if (g != nullptr) { a.ln_gamma = g; a.ln_beta = b; a.ln_out = h->hbuf; a.ln_counters = h->ln_counters; }
-  return launch_gemm_bf16(A, lda, W, K, a, EPI_F32_RESID, s);
-}
-
 // patch GEMM .. projection GEMM: reads h->a0, writes h->emb, touches nothing outside the handle
 static int encode_body(evr_vit* h, int B, cudaStream_t s) {
   const int d = h->cfg.width, L = h->L, P = h->g * h->g, od = h->cfg.out_dim;
@@ -194,23 +180,14 @@ static int encode_body(evr_vit* h, int B, cudaStream_t s) {
   if (launch_cls_rows(h->x, h->cls, h->pos, B, L, d, s)) return 1;
   // ln_pre (fp32 in place: it is the start of the residual stream)
   if (launch_layernorm(h->x, d, h->x, d, 0, h->ln_pre_g, h->ln_pre_b, M, d, s)) return 1;
-  // ln_1 of block 0 is a launch of its own; every later LayerNorm of the stack rides in the residual GEMM before it
-  const bool fuse = ln_fuse_enabled();
-  const size_t nl = h->layers.size();
-  for (size_t li = 0; li < nl; ++li) {
-    const LayerW& l = h->layers[li];
-    if (!fuse || li == 0)
-      if (launch_layernorm(h->x, d, h->hbuf, d, 1, l.ln1_g, l.ln1_b, M, d, s)) return 1;
+  for (const LayerW& l : h->layers) {
+    if (launch_layernorm(h->x, d, h->hbuf, d, 1, l.ln1_g, l.ln1_b, M, d, s)) return 1;
     if (gemm(h->hbuf, d, l.w_in, d, M, 3 * d, l.b_in, h->qkv, 3 * d, EPI_BF16, s)) return 1;
     if (launch_attention(h->qkv, h->attn, B, L, d, h->cfg.heads, 0, s)) return 1;
-    if (gemm_resid_ln(h, h->attn, d, l.w_out, d, M, l.b_out, fuse ? l.ln2_g : nullptr, l.ln2_b, s)) return 1;
-    if (!fuse)
-      if (launch_layernorm(h->x, d, h->hbuf, d, 1, l.ln2_g, l.ln2_b, M, d, s)) return 1;
+    if (gemm(h->attn, d, l.w_out, d, M, d, l.b_out, h->x, d, EPI_F32_RESID, s)) return 1;
+    if (launch_layernorm(h->x, d, h->hbuf, d, 1, l.ln2_g, l.ln2_b, M, d, s)) return 1;
     if (gemm(h->hbuf, d, l.w_fc, d, M, 4 * d, l.b_fc, h->fbuf, 4 * d, EPI_BF16_GELU, s)) return 1;
-    const LayerW* nx = (fuse && li + 1 < nl) ? &h->layers[li + 1] : nullptr;
-    if (gemm_resid_ln(h, h->fbuf, 4 * d, l.w_proj, 4 * d, M, l.b_proj, nx ? nx->ln1_g : nullptr,
-                      nx ? nx->ln1_b : nullptr, s))
-      return 1;
+    if (gemm(h->fbuf, 4 * d, l.w_proj, 4 * d, M, d, l.b_proj, h->x, d, EPI_F32_RESID, s)) return 1;
   }
   // ln_post on the class token, projection, optional L2 normalise
   if (launch_layernorm(h->x, static_cast<size_t>(L) * d, h->cls_ln, d, 1, h->ln_post_g, h->ln_post_b, B, d, s)) return 1;
