@@ -75,6 +75,15 @@ bool pdl_enabled() {
   return on == 1;
 }
 
+bool tail_split_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("EVR_NO_TAILSPLIT");
+    on = (e && e[0] == '1') ? 0 : 1;
+  }
+  return on == 1;
+}
+
 bool graphs_enabled() {
   static int on = -1;
   if (on < 0) {

@@ -69,6 +69,7 @@ struct PerDeviceMax {
 // writes.  Every kernel launched this way calls pdl_wait() before its first access to activations (which also keeps
 // completion transitive along the chain).  EVR_NO_PDL=1 turns the attribute off.
 bool pdl_enabled();
+bool tail_split_enabled();  // gemm_tc.cu: strips for the last round's tiles; EVR_NO_TAILSPLIT=1 turns it off (A/B runs)
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
                               Args&&... args) {

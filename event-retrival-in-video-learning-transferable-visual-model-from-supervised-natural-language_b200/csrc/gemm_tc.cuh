@@ -32,7 +32,32 @@ struct GemmArgs {
   int ldo;
   const float* pos;   // EPI_PATCH: positional_embedding [(P+1), N]
   int patches;        // EPI_PATCH: P
+  // Tail split (set by launch_gemm_bf16).  Tiles are walked round-robin by the persistent units; the tiles of the last,
+  // partly filled round (tiles >= full_tiles) are cut into `tail_split` column strips of BLOCK_N / tail_split so that the
+  // short round costs 1/tail_split of a tile instead of a whole one (600 tiles on 74 pairs: 8.1 rounds -> 8.25, not 9).
+  int full_tiles;     // tiles [0, full_tiles) are whole BLOCK_N-wide tiles
+  int tail_split;     // >= 1; strips per tail tile
 };
+
+// work item -> (tile, first column, width); items [0, full_tiles) are whole tiles, then tail_split strips per tile
+struct GemmItem {
+  int m_idx, n0, width;
+};
+template <int BLOCK_N>
+__device__ __forceinline__ GemmItem gemm_item(int it, int num_n, int full_tiles, int tail_split) {
+  GemmItem g;
+  int tile = it, sub = 0;
+  g.width = BLOCK_N;
+  if (it >= full_tiles) {
+    const int j = it - full_tiles;
+    tile = full_tiles + j / tail_split;
+    sub = j - (j / tail_split) * tail_split;
+    g.width = BLOCK_N / tail_split;
+  }
+  g.m_idx = tile / num_n;  // n-fast: the N tiles of one row block run together, A is read from HBM once
+  g.n0 = (tile - g.m_idx * num_n) * BLOCK_N + sub * g.width;
+  return g;
+}
 
 constexpr int kGemmBlockM = 128;
 constexpr int kGemmBlockK = 64;  // 64 x 16-bit = one 128-B swizzle atom row
@@ -92,7 +117,7 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 template <int BLOCK_N, int EPI, int CG>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-               const GemmArgs args) {
+               const __grid_constant__ CUtensorMap tmap_b_tail, const GemmArgs args) {
   using Cfg = GemmCfg<BLOCK_N, EPI, CG>;
   using Epi = EpiCfg<EPI>;
   constexpr int kStages = Cfg::kStages;
@@ -118,11 +143,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   if constexpr (CG == 2) cluster_sync_relaxed();  // both CTAs resident before the pair-wide TMEM allocation
   const int num_n = (args.N + BLOCK_N - 1) / BLOCK_N;
   const int num_tiles = num_m * num_n;
+  const int num_items = args.full_tiles + (num_tiles - args.full_tiles) * args.tail_split;
   const int num_kb = args.K / kGemmBlockK;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
+    tma_prefetch_desc(&tmap_b_tail);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < kStages; ++i) {
@@ -151,23 +178,26 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       // ===== TMA producer =====
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = unit; tile < num_tiles; tile += num_units) {
-        const int n_idx = tile % num_n, m_idx = tile / num_n;  // n-fast: the N tiles of one row block run together, A is read from HBM once
-        const int a_row = m_idx * kTileM + static_cast<int>(rank) * kGemmBlockM;
-        const int b_row = n_idx * BLOCK_N + static_cast<int>(rank) * Cfg::kBRows;
+      for (int it = unit; it < num_items; it += num_units) {
+        const GemmItem g = gemm_item<BLOCK_N>(it, num_n, args.full_tiles, args.tail_split);
+        const int a_row = g.m_idx * kTileM + static_cast<int>(rank) * kGemmBlockM;
+        const int b_rows = g.width / CG;  // weight rows staged by this CTA
+        const int b_row = g.n0 + static_cast<int>(rank) * b_rows;
+        const CUtensorMap* tb = g.width == BLOCK_N ? &tmap_b : &tmap_b_tail;  // box = b_rows x 64
+        const uint32_t stage_tx = Cfg::kABytes + b_rows * kGemmBlockK * 2;
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * Cfg::kStageBytes;
           uint8_t* sb = sa + Cfg::kABytes;
           if constexpr (CG == 2) {
             tma_load_2d_pair(sa, &tmap_a, &full_bar[stage], kb * kGemmBlockK, a_row, kEvictNormal);
-            tma_load_2d_pair(sb, &tmap_b, &full_bar[stage], kb * kGemmBlockK, b_row, kEvictLast);
-            if (leader) mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes * 2);
+            tma_load_2d_pair(sb, tb, &full_bar[stage], kb * kGemmBlockK, b_row, kEvictLast);
+            if (leader) mbar_expect_tx(&full_bar[stage], stage_tx * 2);
             else mbar_arrive_cluster(&full_bar[stage], 0);
           } else {
-            mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+            mbar_expect_tx(&full_bar[stage], stage_tx);
             tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kGemmBlockK, a_row, kEvictNormal);
-            tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * kGemmBlockK, b_row, kEvictLast);
+            tma_load_2d(sb, tb, &full_bar[stage], kb * kGemmBlockK, b_row, kEvictLast);
           }
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
@@ -176,12 +206,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   } else if (warp == 1) {
     if (leader && elect_one()) {
       // ===== MMA issuer (leader CTA only) =====
-      constexpr uint32_t idesc = umma_idesc_f16(/*bf16*/ 1, kTileM, BLOCK_N);
+      constexpr uint32_t idesc_full = umma_idesc_f16(/*bf16*/ 1, kTileM, BLOCK_N);
+      const uint32_t idesc_tail = umma_idesc_f16(/*bf16*/ 1, kTileM, BLOCK_N / args.tail_split);
       int stage = 0;
       uint32_t phase = 0;
       int as = 0;
       uint32_t aphase = 0;
-      for (int tile = unit; tile < num_tiles; tile += num_units) {
+      for (int it = unit; it < num_items; it += num_units) {
+        const uint32_t idesc = it < args.full_tiles ? idesc_full : idesc_tail;
         mbar_wait(&tmem_empty[as], aphase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * BLOCK_N;
@@ -223,10 +255,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     constexpr int kIters = Epi::kUnitsPerRow;  // 16-B units per lane per chunk: 4 (bf16) | 8 (fp32)
     int as = 0;
     uint32_t aphase = 0;
-    for (int tile = unit; tile < num_tiles; tile += num_units) {
-      const int n_idx = tile % num_n, m_idx = tile / num_n;  // n-fast: the N tiles of one row block run together, A is read from HBM once
-      const int row0 = m_idx * kTileM + static_cast<int>(rank) * kGemmBlockM + q * 32;  // first row of this warp
-      const int col_base = n_idx * BLOCK_N + hsel * kEpiCols;
+    for (int it = unit; it < num_items; it += num_units) {
+      const GemmItem g = gemm_item<BLOCK_N>(it, num_n, args.full_tiles, args.tail_split);
+      const int row0 = g.m_idx * kTileM + static_cast<int>(rank) * kGemmBlockM + q * 32;  // first row of this warp
+      const int col_base = g.n0 + hsel * kEpiCols;
+      const int n_lim = min(args.N, g.n0 + g.width);  // columns of this item (a tail strip is narrower than BLOCK_N)
       // this tile's bias values for the warp's columns go to shared memory while the MMAs are still running; the chunk
       // loop then reads them as broadcast ld.shared (a global/L2 round trip per chunk sat on the critical path: ncu
       // showed the bias FADDs as the top long_scoreboard stall of the epilogue)
@@ -234,7 +267,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         if (lane < kChunks * 8) {
           const int col = col_base + (lane >> 3) * 64 + (lane & 7) * 4;
           float4 bb = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (col < args.N) bb = __ldg(reinterpret_cast<const float4*>(args.bias + col));
+          if (col < n_lim) bb = __ldg(reinterpret_cast<const float4*>(args.bias + col));
           *reinterpret_cast<float4*>(bias_s + lane * 4) = bb;
         }
         __syncwarp();
@@ -259,7 +292,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             else mbar_arrive_cluster(&tmem_empty[as], 0);
           }
         }
-        if (col0 < args.N) {  // warp-uniform (N is a multiple of 32)
+        if (col0 < n_lim) {  // warp-uniform (N and the strip width are multiples of 32)
           float f[32];
 #pragma unroll
           for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[c & 1][j]);
@@ -298,7 +331,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             const int u = it * 32 + lane;
             const int r = u / Epi::kUnitsPerRow, cu = u % Epi::kUnitsPerRow;
             const int row = row0 + r, col = col0 + cu * kColsPerUnit;
-            if (row < args.M && col < args.N) {
+            if (row < args.M && col < n_lim) {
               const uint4 sv = *reinterpret_cast<const uint4*>(stage + r * Epi::kPitch + cu * 16);
               if constexpr (Epi::kOutBf16) {
                 *reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(args.out) + static_cast<size_t>(row) * args.ldo + col) = sv;
