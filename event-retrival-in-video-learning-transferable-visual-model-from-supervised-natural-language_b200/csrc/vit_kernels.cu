@@ -634,9 +634,11 @@ int launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L,
       EVR_CHECK_CUDA(cudaFuncSetAttribute(attention_short_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           2 * kAttnStageBytes));
     }
-    const int items = B * heads, slots = sm_count() * 4;        // 4 CTAs (2 x 27 KB stages each) per SM
-    const int per_cta = (items + slots - 1) / slots;
-    const int grid = (items + per_cta - 1) / per_cta;           // every CTA walks the same number of items (+-1)
+    // 4 CTAs (2 x 27 KB stages each) per SM, all resident; item i goes to CTA i mod grid, so with grid = 4 x SMs every SM
+    // walks items / SMs (+-1) of them (3072 items: 20-21 per SM; sizing the grid for equal items per CTA instead left
+    // 512 CTAs of 6 items = 24 on the SMs that got four CTAs and 18 on the others)
+    const int items = B * heads, slots = sm_count() * 4;
+    const int grid = items < slots ? items : slots;
     ProfScope ps(PF_ATTN, stream);
     EVR_CHECK_CUDA(launch_pdl(L == 50 ? attention_short_kernel<50> : attention_short_kernel<0>, dim3(grid), dim3(128),
                               2 * kAttnStageBytes, stream, qkv, out, L, d, heads, items,
