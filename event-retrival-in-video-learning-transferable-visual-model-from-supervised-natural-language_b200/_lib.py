@@ -74,7 +74,9 @@ PROFILE_FAMILIES = ("gemm_tc", "attention", "layernorm", "vit_misc", "topk_scan"
 
 
 def profile_enable(on):
-    check(lib.evr_profile_enable(1 if on else 0), "evr_profile_enable")
+    """True / 1: CUDA events around every launch (all families).  2: no events, the GEMM kernel stamps %globaltimer
+    itself (its launches timed in place, PDL overlap intact).  False / 0: off."""
+    check(lib.evr_profile_enable(2 if on == 2 else (1 if on else 0)), "evr_profile_enable")
 
 
 def profile_read():

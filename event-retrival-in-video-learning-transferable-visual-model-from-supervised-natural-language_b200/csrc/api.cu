@@ -167,6 +167,24 @@ void prof_end(void* token, cudaStream_t s) {
   std::lock_guard<std::mutex> lk(g_prof_mu);
   g_prof.push_back(r);
 }
+// device-timer slots: pool[2 i] = min start, pool[2 i + 1] = max end of launch i
+static constexpr int kProfSlots = 16384;
+static unsigned long long* g_dt_pool = nullptr;
+static std::atomic<int> g_dt_used{0};
+unsigned long long* prof_device_slot() {
+  if (g_profile_on.load(std::memory_order_relaxed) != 2 || g_dt_pool == nullptr) return nullptr;
+  const int i = g_dt_used.fetch_add(1, std::memory_order_relaxed);
+  return i < kProfSlots ? g_dt_pool + 2 * i : nullptr;
+}
+static int prof_device_reset() {
+  if (g_dt_pool == nullptr) EVR_CHECK_CUDA(cudaMalloc(&g_dt_pool, 2 * kProfSlots * sizeof(unsigned long long)));
+  std::vector<unsigned long long> init(2 * kProfSlots);
+  for (int i = 0; i < kProfSlots; ++i) { init[2 * i] = ~0ull; init[2 * i + 1] = 0ull; }
+  EVR_CHECK_CUDA(cudaMemcpy(g_dt_pool, init.data(), init.size() * sizeof(unsigned long long), cudaMemcpyHostToDevice));
+  g_dt_used.store(0);
+  return 0;
+}
+
 static void prof_clear() {
   std::lock_guard<std::mutex> lk(g_prof_mu);
   for (ProfRec* r : g_prof) {
@@ -175,6 +193,7 @@ static void prof_clear() {
     delete r;
   }
   g_prof.clear();
+  g_dt_used.store(0);
 }
 
 }  // namespace evr
@@ -182,7 +201,10 @@ static void prof_clear() {
 extern "C" {
 int evr_profile_enable(int on) {
   evr::prof_clear();
-  evr::g_profile_on.store(on ? 1 : 0);
+  if (on == 2) {
+    if (int r = evr::prof_device_reset()) return r;
+  }
+  evr::g_profile_on.store(on == 2 ? 2 : (on ? 1 : 0));
   return 0;
 }
 int evr_profile_read(double* ms_by_family, int64_t* launches_by_family, int n) {
@@ -196,6 +218,19 @@ int evr_profile_read(double* ms_by_family, int64_t* launches_by_family, int n) {
     EVR_CHECK_CUDA(cudaEventElapsedTime(&ms, r->e0, r->e1));
     ms_by_family[r->family] += ms;
     launches_by_family[r->family] += 1;
+  }
+  // device-timer mode: GEMM launches stamped by the kernel itself
+  const int used = evr::g_dt_used.load() < evr::kProfSlots ? evr::g_dt_used.load() : evr::kProfSlots;
+  if (evr::g_dt_pool != nullptr && used > 0) {
+    EVR_CHECK_CUDA(cudaDeviceSynchronize());
+    std::vector<unsigned long long> t(2 * static_cast<size_t>(used));
+    EVR_CHECK_CUDA(cudaMemcpy(t.data(), evr::g_dt_pool, t.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    for (int i = 0; i < used; ++i) {
+      if (t[2 * i + 1] > t[2 * i]) {
+        ms_by_family[evr::PF_GEMM] += static_cast<double>(t[2 * i + 1] - t[2 * i]) * 1e-6;
+        launches_by_family[evr::PF_GEMM] += 1;
+      }
+    }
   }
   return 0;
 }

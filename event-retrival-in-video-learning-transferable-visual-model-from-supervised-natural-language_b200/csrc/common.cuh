@@ -105,11 +105,14 @@ enum ProfFamily : int {
 extern std::atomic<int> g_profile_on;
 void prof_begin(int family, cudaStream_t s, void** token);
 void prof_end(void* token, cudaStream_t s);
+// evr_profile_enable(2): no events; the GEMM kernel stamps %globaltimer itself (GemmArgs::prof).  Returns the slot of
+// the next launch, or nullptr when that mode is off / the pool is used up.
+unsigned long long* prof_device_slot();
 struct ProfScope {
   void* token = nullptr;
   cudaStream_t s;
   ProfScope(int family, cudaStream_t stream) : s(stream) {
-    if (g_profile_on.load(std::memory_order_relaxed)) prof_begin(family, stream, &token);
+    if (g_profile_on.load(std::memory_order_relaxed) == 1) prof_begin(family, stream, &token);
   }
   ~ProfScope() {
     if (token) prof_end(token, s);

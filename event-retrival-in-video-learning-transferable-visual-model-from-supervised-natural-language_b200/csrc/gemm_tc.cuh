@@ -37,6 +37,9 @@ struct GemmArgs {
   // short round costs 1/tail_split of a tile instead of a whole one (600 tiles on 74 pairs: 8.1 rounds -> 8.25, not 9).
   int full_tiles;     // tiles [0, full_tiles) are whole BLOCK_N-wide tiles
   int tail_split;     // >= 1; strips per tail tile
+  // evr_profile_enable(2): [0] = earliest %globaltimer at which a CTA got past pdl_wait, [1] = latest CTA exit; nullptr
+  // otherwise.  Times the launch in place (PDL overlap intact), without a stream operation between the kernels.
+  unsigned long long* prof;
 };
 
 // work item -> (tile, first column, width); items [0, full_tiles) are whole tiles, then tail_split strips per tile
@@ -172,6 +175,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   pdl_wait();  // everything above overlapped the previous kernel's tail; activations are touched only below
+  if (args.prof != nullptr && threadIdx.x == 0) atomicMin(args.prof, globaltimer_ns());
 
   if (warp == 0) {
     if (elect_one()) {
@@ -370,6 +374,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     if constexpr (CG == 2) tmem_dealloc_pair<Cfg::kTmemCols>(tmem_base);
     else tmem_dealloc<Cfg::kTmemCols>(tmem_base);
   }
+  if (args.prof != nullptr && threadIdx.x == 0) atomicMax(args.prof + 1, globaltimer_ns());
 }
 
 // host launcher (gemm_tc.cu)

@@ -159,6 +159,12 @@ __device__ __forceinline__ uint64_t umma_smem_desc_sw128(uint32_t smem_addr) {
 }
 // Instruction descriptor for kind::f16: fp32 accumulate, A and B K-major.
 // fmt: 0 = fp16, 1 = bf16.
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
 __host__ __device__ constexpr uint32_t umma_idesc_f16(uint32_t fmt, uint32_t M, uint32_t N) {
   return (1u << 4)            // c_format = F32
          | (fmt << 7)         // a_format

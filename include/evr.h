@@ -23,7 +23,10 @@ int64_t evr_launch_count(void);
 /* Per-kernel-family device timing for the roofline report (bench.py): evr_profile_enable(1) clears the records and
  * makes every launch site bracket its kernel with CUDA events on the launching stream; evr_profile_read sums them.
  * Families: 0 tcgen05 GEMM, 1 attention core, 2 LayerNorm, 3 other ViT kernels, 4 fused scan+top-k,
- * 5 final select/merge, 6 store prepare / re-score.  n >= 7. */
+ * 5 final select/merge, 6 store prepare / re-score.  n >= 7.
+ * evr_profile_enable(2): no events (an event between two kernels costs ~5 us and breaks their programmatic overlap);
+ * instead every GEMM launch records, on the device, the earliest %globaltimer at which one of its CTAs got past
+ * griddepcontrol.wait and the latest CTA exit; evr_profile_read then reports family 0 from those stamps. */
 int evr_profile_enable(int on);
 int evr_profile_read(double* ms_by_family, int64_t* launches_by_family, int n);
 

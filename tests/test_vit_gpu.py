@@ -209,3 +209,24 @@ def test_small_batch_graph_replay_is_identical(pkg, cuda, b32):
         on_side = enc.encode(b).clone()
     s.synchronize()
     assert torch.equal(on_side, replay_b)
+
+
+def test_profile_modes_do_not_change_results(pkg, cuda, b32):
+    """evr_profile_enable(1) brackets launches with events, (2) lets the GEMM kernel stamp %globaltimer: same outputs,
+    the same number of GEMM launches reported by both, positive times."""
+    visual, u8, pix, ref = b32
+    enc = pkg.vit.VisionEncoder.from_state_dict(visual.state_dict(), "ViT-B/32", device=cuda, max_batch=64)
+    x = pix[:40].to(cuda)  # above the captured-graph batch limit: plain launches in every mode
+    base = enc.encode(x).clone()
+    counts = {}
+    for mode in (1, 2):
+        pkg._lib.profile_enable(mode)
+        out = enc.encode(x).clone()
+        torch.cuda.synchronize()
+        fam = pkg._lib.profile_read()
+        pkg._lib.profile_enable(False)
+        assert torch.equal(out, base)
+        ms, n = fam["gemm_tc"]
+        assert n == 2 + 4 * 12 and ms > 0.0, (mode, fam)  # patch + projection + 4 per block
+        counts[mode] = fam
+    assert counts[2]["layernorm"][1] == 0 and counts[1]["layernorm"][1] == 2 + 2 * 12  # events only in mode 1
