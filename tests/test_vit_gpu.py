@@ -230,3 +230,22 @@ def test_profile_modes_do_not_change_results(pkg, cuda, b32):
         assert n == 2 + 4 * 12 and ms > 0.0, (mode, fam)  # patch + projection + 4 per block
         counts[mode] = fam
     assert counts[2]["layernorm"][1] == 0 and counts[1]["layernorm"][1] == 2 + 2 * 12  # events only in mode 1
+
+
+def test_gemm_bits_do_not_depend_on_tile_width(pkg, cuda, monkeypatch):
+    """The tile chooser (width 128 / 192 / 256, tail strips) is free to change with the batch: an output element is
+    the same K-ordered sum in every tiling, so the bits must not move (this is what keeps a frame's embedding
+    independent of the batch it was encoded in)."""
+    g = torch.Generator().manual_seed(11)
+    M, N, K = 3000, 768, 768
+    A = (torch.randn(M, K, generator=g) * 0.5).to(cuda).bfloat16()
+    W = (torch.randn(N, K, generator=g) * 0.05).to(cuda).bfloat16()
+    bias = torch.randn(N, generator=g).to(cuda)
+    outs = []
+    for bn in ("128", "192", "256"):
+        monkeypatch.setenv("EVR_GEMM_BN", bn)
+        out = torch.empty((M, N), dtype=torch.float32, device=cuda)
+        _gemm(pkg, A, W, bias, out, 3)
+        outs.append(out)
+    monkeypatch.delenv("EVR_GEMM_BN")
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
