@@ -19,6 +19,9 @@ import time
 import numpy as np
 import torch
 
+from collections import deque
+from concurrent.futures import ThreadPoolExecutor
+
 from . import clip as _clip
 from .preprocess import GpuPreprocess
 from .search import FrameStore
@@ -147,6 +150,39 @@ class DataService:
             return []
 
 
+def decode_frames(paths, workers=None, window=None):
+    """Ordered, bounded-lookahead JPEG decode on host threads: yields `np.uint8 [H, W, 3]` (or the exception that the
+    decode raised) for every path, in order.  The reference decodes one frame at a time on the request thread
+    (`Image.open(p).convert('RGB')`, embedding_service.py:475); PIL's decoder releases the GIL, so `workers` threads give
+    the same pixels `workers` times faster, and at most `window` decoded frames wait for the GPU at any time."""
+    from PIL import Image
+
+    def one(path):
+        try:
+            return np.array(Image.open(path).convert('RGB'))
+        except Exception as e:  # the caller turns this into a zero row (embedding_service.py:477-480)
+            return e
+
+    workers = min(16, os.cpu_count() or 1) if workers is None else int(workers)
+    if workers <= 1:
+        for path in paths:
+            yield one(path)
+        return
+    window = window or 4 * workers
+    with ThreadPoolExecutor(max_workers=workers) as pool:
+        queue, it = deque(), iter(paths)
+        for path in it:
+            queue.append(pool.submit(one, path))
+            if len(queue) >= window:
+                break
+        while queue:
+            frame = queue.popleft().result()
+            nxt = next(it, None)
+            if nxt is not None:
+                queue.append(pool.submit(one, nxt))
+            yield frame
+
+
 class EmbeddingService:
     """Drop-in for Backend/services/embedding_service.py:EmbeddingService (same constructor positionals).
 
@@ -166,6 +202,7 @@ class EmbeddingService:
         self._load_kwargs = dict(load_kwargs or {})
         self.text_encoder = text_encoder
         self.gpu_preprocess = bool(gpu_preprocess)
+        self.decode_workers = None  # host threads decoding JPEGs during ingest (None: min(16, cores); 1: serial)
         self.original_model, self.preprocess = self._clip.load(model_name, device=device, **self._load_kwargs)
         self.finetuned_model = None
         self.active_model = "original"
@@ -386,25 +423,35 @@ class EmbeddingService:
             # (preprocess.py) and ToTensor + Normalize are fused into the encoder's im2col.  Frames of one size are
             # batched together; the row order stays the sorted file order.
             pre = self._gpu_pre = getattr(self, "_gpu_pre", None) or GpuPreprocess(S, self.device)
-            pending, shape = [], None
+            shape, stage, stage_np, count = None, None, None, 0
+            stages = self._ingest_stages = getattr(self, "_ingest_stages", None) or {}  # pinned once, kept across calls
 
             def flush():
-                if pending:
-                    u8 = pre(np.stack(pending))
-                    all_embeddings.append(self._encode_images(u8, key))
-                    pending.clear()
+                nonlocal count
+                if count:
+                    u8 = pre(stage[:count])  # pinned -> device, resize + crop on the GPU
+                    all_embeddings.append(self._encode_images(u8, key))  # returns host rows: the stage is free again
+                    count = 0
 
-            for i, name in enumerate(frame_files):
-                try:
-                    frame = np.array(Image.open(os.path.join(folder_path, name)).convert('RGB'))
-                except Exception as e:
-                    print(f"Error preprocessing image {name}: {e}")
+            paths = [os.path.join(folder_path, name) for name in frame_files]
+            for i, frame in enumerate(decode_frames(paths, self.decode_workers)):
+                if isinstance(frame, Exception):
+                    print(f"Error preprocessing image {frame_files[i]}: {frame}")
                     frame = np.zeros(shape or (S, S, 3), dtype=np.uint8)
                     bad_rows.append(i)
-                if frame.shape != shape or len(pending) == 256:
+                if frame.shape != shape or count == stage.shape[0]:
                     flush()
-                    shape = frame.shape
-                pending.append(frame)
+                    if frame.shape != shape:  # frames of one size share a pinned staging batch (one per ingest, usually)
+                        shape = frame.shape
+                        stage = stages.get(shape)
+                        if stage is None:
+                            if len(stages) >= 2:
+                                stages.clear()
+                            # 64 frames per staging batch: page-locking costs ~1 ms per MB, a 720p batch is 177 MB
+                            stage = stages[shape] = torch.empty((64,) + shape, dtype=torch.uint8).pin_memory()
+                        stage_np = stage.numpy()
+                stage_np[count] = frame  # numpy memcpy (releases the GIL; torch's copy_ would spin up its thread pool)
+                count += 1
             flush()
         else:
             batch_size = 32  # :461

@@ -126,3 +126,44 @@ def test_clip_face_fails_loudly_without_weights_or_gpu(tmp_path):
         clip.load("ViT-B/32", device="cpu", random_init=1)
     sd = clip.random_visual_state_dict("ViT-B/32", seed=1)
     assert sum(v.numel() for k, v in sd.items() if k.startswith("visual.")) == 87_849_216
+
+
+def test_threaded_decode_is_ordered_bounded_and_identical(services, tmp_path):
+    """Ingest decodes on host threads (services.decode_frames): same pixels as the reference's serial
+    `Image.open(p).convert('RGB')` (embedding_service.py:475), yielded in path order, a bad file comes back as the
+    exception (-> zero row), and no more than `window` frames are ever decoded ahead of the consumer."""
+    import numpy as np
+    from PIL import Image
+    rng = np.random.default_rng(0)
+    paths = []
+    for i in range(23):
+        p = tmp_path / f"{i:04d}.jpg"
+        Image.fromarray(rng.integers(0, 256, (40 + i, 64, 3), dtype=np.uint8)).save(p, quality=90)
+        paths.append(str(p))
+    bad = tmp_path / "0007.jpg"
+    bad.write_bytes(b"not a jpeg")
+    serial = list(services.decode_frames(paths, workers=1))
+    threaded = list(services.decode_frames(paths, workers=4, window=5))
+    assert len(serial) == len(threaded) == 23
+    for i, (a, b) in enumerate(zip(serial, threaded)):
+        if i == 7:
+            assert isinstance(a, Exception) and isinstance(b, Exception)
+        else:
+            assert a.shape == (40 + i, 64, 3) and np.array_equal(a, b)
+            assert np.array_equal(a, np.array(Image.open(paths[i]).convert('RGB')))
+    # bounded lookahead: after consuming one frame at most `window` more have been opened
+    opened = []
+    real_open = Image.open
+
+    def spy(path, *a, **k):
+        opened.append(path)
+        return real_open(path, *a, **k)
+    Image.open = spy
+    try:
+        gen = services.decode_frames(paths, workers=2, window=3)
+        next(gen)
+        time.sleep(0.3)
+        assert len(opened) <= 1 + 3
+        gen.close()
+    finally:
+        Image.open = real_open
