@@ -257,3 +257,40 @@ def test_search_by_image(tmp_path, cuda, visual, full_sd):
     assert qs.search_by_image(svc, Image.open(query), -1.0, 1, fmt, "vid", ps.video_data_mapping)[0]["id"] == 7
     assert qs.search_by_image(svc, "http://example.com/x.jpg", 0.0, 3, fmt, "vid", ps.video_data_mapping) == []
     assert qs.search_by_image(svc, str(tmp_path / "missing.jpg"), 0.0, 3, fmt, "vid", ps.video_data_mapping) == []
+
+
+def test_finetuned_checkpoint_switch(tmp_path, cuda, full_sd):
+    """`"model": "finetuned"` (embedding_service.py:93-120): a checkpoint written the way the reference's training
+    script writes it -- {'model_state_dict': CLIPWithClassifier.state_dict()} = `clip_model.*` keys + the classifier
+    head -- is loaded into the B200 tower; ingest with the fine-tuned model differs from the original one and equals
+    the oracle run on the fine-tuned weights (forward = encode_image -> fp32 -> L2 normalise, :36-49)."""
+    services = importlib.import_module(PKG + ".services")
+    tuned = vo.build_visual("ViT-B/32", seed=77)             # "fine-tuned" vision weights: another seed
+    ckpt = {"clip_model.visual." + k: v.clone() for k, v in tuned.state_dict().items()}
+    ckpt["clip_model.logit_scale"] = torch.tensor(2.6592)
+    ckpt["logit_scale"] = torch.tensor(2.6592)
+    ckpt.update({"classifier.0.weight": torch.zeros(512, 512), "classifier.0.bias": torch.zeros(512),
+                 "classifier.3.weight": torch.zeros(3, 512), "classifier.3.bias": torch.zeros(3)})
+    path = str(tmp_path / "final_checkpoint.pt")
+    torch.save({"model_state_dict": ckpt, "epoch": 3}, path)
+
+    names = [f"{i}.png" for i in (3, 1, 2, 10)]
+    svc, ps = _site(tmp_path, full_sd, {"vid": names})
+    assert svc.set_active_model("finetuned") is False        # nothing loaded yet
+    svc._load_finetuned_model(path)
+    assert svc.set_active_model("finetuned") is True and svc.get_active_model_name() == "finetuned"
+    folder = os.path.join(str(tmp_path), "frames", "vid")
+    out_ft = np.load(svc.extract_and_save_embeddings_from_folder(folder, "finetuned", "vid"))
+    out_or = np.load(svc.extract_and_save_embeddings_from_folder(folder, "original", "vid"))
+    order = sorted(names)
+    ref_ft = _oracle_rows(tuned, svc, folder, order)
+    cos = (out_ft.astype(np.float32) * ref_ft).sum(-1)
+    assert cos.min() >= 0.999, cos
+    assert ((out_ft.astype(np.float32) * out_or.astype(np.float32)).sum(-1) < 0.9).all()  # really another model
+    meta = json.load(open(ps.get_metadata_path("vid")))
+    assert all(item["embedding_model"] == "original" for item in meta)  # stamped by the last ingest
+    # constructor path: EmbeddingService(checkpoint_path=...) loads it at start-up like :96-101
+    cs = services.CacheService()
+    svc2 = services.EmbeddingService(cs, ps, services.DataService(ps, cs), "cuda",
+                                     load_kwargs=dict(state_dict=full_sd, max_batch=64), checkpoint_path=path)
+    assert svc2.finetuned_model is not None and svc2.set_active_model("finetuned") is True
