@@ -11,6 +11,7 @@ The CUDA library (lib/libevr.so, built by __graft_entry__.build()) is required; 
 """
 from . import _lib  # noqa: F401  (fails loudly if libevr.so is missing)
 from . import search, text, vit  # noqa: F401
-from . import clip, embedding, preprocess, query_strategies, services, store  # noqa: F401
+from . import clip, embedding, preprocess, query_strategies, scenecut, services, store  # noqa: F401
 
-__all__ = ["search", "vit", "text", "clip", "embedding", "preprocess", "query_strategies", "services", "store", "_lib"]
+__all__ = ["search", "vit", "text", "clip", "embedding", "preprocess", "query_strategies", "scenecut", "services",
+           "store", "_lib"]

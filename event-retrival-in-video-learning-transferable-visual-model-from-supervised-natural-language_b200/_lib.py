@@ -49,6 +49,7 @@ SIGNATURES = {
     "evr_vit_encode": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_int, c_int, c_void_p]),
     "evr_resize_crop_u8": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p,
                                    c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "evr_scene_deltas": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "evr_text_create": (c_int, [ctypes.POINTER(TextCfg), ctypes.POINTER(c_void_p), c_int, c_int,
                                 ctypes.POINTER(c_void_p)]),
     "evr_text_destroy": (c_int, [c_void_p]),

@@ -108,6 +108,18 @@ int evr_resize_crop_u8(const uint8_t* src, int B, int H, int W, int S, const int
                        int hksize, const int32_t* vbounds, const int32_t* vk, int vksize, int y0, int rows,
                        uint8_t* tmp, uint8_t* dst, void* stream);
 
+/* ---- scene-cut scoring -----------------------------------------------------------------
+ * replaces  the per-frame work of PySceneDetect's ContentDetector behind
+ *           scene_manager.detect_scenes(frame_source=video_manager)   Backend/segment_video.py:9-13
+ *           (cv2.cvtColor(frame, COLOR_BGR2HSV); per channel np.sum(np.abs(curr - last)))
+ * frames [T, H, W, 3] uint8 decoded frames (bgr != 0: OpenCV's B,G,R order; 0: R,G,B), consecutive in time.
+ * sums [T-1, 3] (zeroed by the call): for the pair (t, t+1) the sums over the pixels of frame[::downscale, ::downscale]
+ * of |dH|, |dS|, |dV| of OpenCV's 8-bit HSV (H in 0..179), exact integers.  sdiv_table / hdiv_table: OpenCV's
+ * 12-bit fixed-point division tables (256 int32 each, device memory; scenecut.py builds them as color_hsv does).
+ * The threshold / min_scene_len rule and the scene list are host logic (scenecut.py). */
+int evr_scene_deltas(const uint8_t* frames, int T, int H, int W, int bgr, int downscale, const int32_t* sdiv_table,
+                     const int32_t* hdiv_table, unsigned long long* sums, void* stream);
+
 /* ---- CLIP text tower (encode_text) ---------------------------------------------------
  * replaces  model.encode_text(clip.tokenize([query]))   Backend/services/embedding_service.py:169-177
  *           (openai/CLIP CLIP.encode_text: causal transformer, EOT row, @ text_projection)
