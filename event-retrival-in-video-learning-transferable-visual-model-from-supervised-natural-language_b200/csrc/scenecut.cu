@@ -91,6 +91,85 @@ scene_delta_kernel(const uint8_t* __restrict__ frames, int H, int W, int bgr, in
   }
 }
 
+// Aligned full-resolution path: a thread keeps its 4-pixel groups and walks them through kChunk consecutive frame
+// pairs, so every frame is read once and converted to HSV once per chunk (the pair kernel converts each frame twice);
+// the HSV of the previous frame stays packed in registers (h | s << 8 | v << 16).  grid (x, ceil(pairs / kChunk)).
+constexpr int kChunk = 8;
+
+__device__ __forceinline__ uint32_t hsv_packed(int c0, int c1, int c2, int bgr, const int* sdiv, const int* hdiv) {
+  const Hsv p = hsv_u8(c0, c1, c2, bgr, sdiv, hdiv);
+  return static_cast<uint32_t>(p.h) | (static_cast<uint32_t>(p.s) << 8) | (static_cast<uint32_t>(p.v) << 16);
+}
+struct Words3 {
+  uint32_t a0, a1, a2;  // 4 pixels = 12 bytes
+};
+__device__ __forceinline__ Words3 load_group(const uint32_t* w, int gi) {
+  Words3 r;
+  r.a0 = __ldg(w + 3 * gi);
+  r.a1 = __ldg(w + 3 * gi + 1);
+  r.a2 = __ldg(w + 3 * gi + 2);
+  return r;
+}
+__device__ __forceinline__ void hsv_group(const Words3& w, int bgr, const int* sdiv, const int* hdiv, uint32_t (&o)[4]) {
+  o[0] = hsv_packed(w.a0 & 255, (w.a0 >> 8) & 255, (w.a0 >> 16) & 255, bgr, sdiv, hdiv);
+  o[1] = hsv_packed(w.a0 >> 24, w.a1 & 255, (w.a1 >> 8) & 255, bgr, sdiv, hdiv);
+  o[2] = hsv_packed((w.a1 >> 16) & 255, w.a1 >> 24, w.a2 & 255, bgr, sdiv, hdiv);
+  o[3] = hsv_packed((w.a2 >> 8) & 255, (w.a2 >> 16) & 255, w.a2 >> 24, bgr, sdiv, hdiv);
+}
+
+__global__ void __launch_bounds__(256)
+scene_walk_kernel(const uint8_t* __restrict__ frames, int H, int W, int pairs, int bgr, const int* __restrict__ sdiv_g,
+                  const int* __restrict__ hdiv_g, unsigned long long* __restrict__ sums) {
+  __shared__ int sdiv[256], hdiv[256];
+  __shared__ unsigned long long red[kChunk][3];
+  sdiv[threadIdx.x] = sdiv_g[threadIdx.x];
+  hdiv[threadIdx.x] = hdiv_g[threadIdx.x];
+  if (threadIdx.x < kChunk * 3) (&red[0][0])[threadIdx.x] = 0ull;
+  __syncthreads();
+  const size_t frame_words = static_cast<size_t>(H) * W * 3 / 4;
+  const int t0 = blockIdx.y * kChunk, nt = min(kChunk, pairs - t0);
+  const uint32_t* base = reinterpret_cast<const uint32_t*>(frames) + t0 * frame_words;
+  const int groups = (H * W) >> 2;
+  int acc[kChunk][3];
+#pragma unroll
+  for (int t = 0; t < kChunk; ++t) acc[t][0] = acc[t][1] = acc[t][2] = 0;
+  for (int gi = blockIdx.x * blockDim.x + threadIdx.x; gi < groups; gi += gridDim.x * blockDim.x) {
+    uint32_t prev[4], cur[4];
+    hsv_group(load_group(base, gi), bgr, sdiv, hdiv, prev);
+    Words3 nxt = load_group(base + frame_words, gi);  // nt >= 1; the loads run one frame ahead of the arithmetic
+#pragma unroll
+    for (int t = 0; t < kChunk; ++t) {
+      if (t < nt) {
+        const Words3 w = nxt;
+        if (t + 1 < nt) nxt = load_group(base + (t + 2) * frame_words, gi);
+        hsv_group(w, bgr, sdiv, hdiv, cur);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const uint32_t d = __vabsdiffu4(prev[k], cur[k]);  // per-byte |dh|, |ds|, |dv|
+          acc[t][0] += d & 255;
+          acc[t][1] += (d >> 8) & 255;
+          acc[t][2] += d >> 16;
+          prev[k] = cur[k];
+        }
+      }
+    }
+  }
+  const int lane = threadIdx.x & 31;
+#pragma unroll
+  for (int t = 0; t < kChunk; ++t) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      int v = acc[t][c];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0 && t < nt) atomicAdd(&red[t][c], static_cast<unsigned long long>(v));
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < nt * 3)
+    atomicAdd(sums + 3 * static_cast<size_t>(t0) + threadIdx.x, (&red[0][0])[threadIdx.x]);
+}
+
 }  // namespace
 }  // namespace evr
 
@@ -115,8 +194,19 @@ extern "C" int evr_scene_deltas(const uint8_t* frames, int T, int H, int W, int 
   if (bx > cap) bx = cap;
   if (bx < 1) bx = 1;
   ProfScope ps(PF_STORE, s);
-  scene_delta_kernel<<<dim3(static_cast<unsigned>(bx), T - 1), 256, 0, s>>>(frames, H, W, bgr ? 1 : 0, downscale,
-                                                                            vec, sdiv_table, hdiv_table, sums);
+  if (vec && T - 1 >= 4) {
+    // one wave: x blocks per chunk row so that x * rows ~ 8 blocks per SM
+    const int rows = (T - 1 + kChunk - 1) / kChunk;
+    long long wx = (cap + rows - 1) / rows;
+    const long long need = (work + 255) / 256;
+    if (wx > need) wx = need;
+    if (wx < 1) wx = 1;
+    scene_walk_kernel<<<dim3(static_cast<unsigned>(wx), rows), 256, 0, s>>>(frames, H, W, T - 1, bgr ? 1 : 0, sdiv_table,
+                                                                           hdiv_table, sums);
+  } else {
+    scene_delta_kernel<<<dim3(static_cast<unsigned>(bx), T - 1), 256, 0, s>>>(frames, H, W, bgr ? 1 : 0, downscale, vec,
+                                                                              sdiv_table, hdiv_table, sums);
+  }
   EVR_CHECK_LAUNCH();
   return 0;
 }

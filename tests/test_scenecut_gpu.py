@@ -17,7 +17,8 @@ def scenecut(pkg):
     return importlib.import_module(PKG + ".scenecut")
 
 
-@pytest.mark.parametrize("T,H,W", [(6, 72, 96), (5, 37, 41), (3, 1, 1), (2, 720, 1280), (4, 5, 3)])
+@pytest.mark.parametrize("T,H,W", [(6, 72, 96), (5, 37, 41), (3, 1, 1), (2, 720, 1280), (4, 5, 3), (38, 36, 64),
+                                   (17, 2, 2), (5, 720, 1280)])
 @pytest.mark.parametrize("order", ["bgr", "rgb"])
 @pytest.mark.parametrize("downscale", [1, 2, 3])
 def test_delta_sums_bit_exact(scenecut, cuda, T, H, W, order, downscale):
