@@ -509,6 +509,52 @@ class _FinetunedImageEncoder:
         return self
 
 
+def frame_metadata_items(folder_path, output_json_path, path_video):
+    """Detector-free stand-in for `process_images_in_folder(folder_path, output_json_path, path_video)`
+    (JSON_sample_DOC.py:90): the same item layout (:74-84) with empty OCR / object lists -- EasyOCR and YOLO are outside
+    this path -- written in sorted frame order so that item i describes embedding row i."""
+    import uuid
+    from PIL import Image
+    items = []
+    for name in sorted(f for f in os.listdir(folder_path) if f.lower().endswith(('.png', '.jpg', '.jpeg'))):
+        path = os.path.join(folder_path, name)
+        with Image.open(path) as im:
+            width, height = im.size
+        stem = os.path.splitext(name)[0]
+        items.append({"id": str(uuid.uuid4()), "media_type": "image", "filepath": path, "tags": ["MainData"],
+                      "metadata": {"width": width, "height": height}, "video": path_video, "frameid": name,
+                      "text_detections": {"detections": []}, "object_detections": {"detections": []},
+                      "frameidx": int(stem) if stem.isdigit() else None})
+    os.makedirs(os.path.dirname(output_json_path) or ".", exist_ok=True)
+    with open(output_json_path, "w", encoding="utf-8") as f:
+        json.dump(items, f, ensure_ascii=False, indent=4)
+    return output_json_path
+
+
+def ingest_video(embedding_service, video_path, video_name=None, model_name="original", threshold=30.0,
+                 metadata_builder=frame_metadata_items):
+    """The processing half of `api_upload_video` (app.py:636-659) without Flask: scene-cut key-frames
+    (`extract_frames_from_video(path, frame_dir, threshold=30.0)`, :638) -> embeddings (`:644`) -> metadata (`:647`) ->
+    `video_mapping.json` entry with the reference's five fields (`:650-659`).  Returns the mapping entry.
+    `metadata_builder(frame_dir, metadata_path, video_path)` is the hook for the reference's OCR / YOLO pass."""
+    from . import scenecut
+    ps = embedding_service.path_service
+    video_name = video_name or os.path.splitext(os.path.basename(video_path))[0]
+    frame_dir = os.path.join(ps.base_dir, video_name)
+    os.makedirs(frame_dir, exist_ok=True)
+    scenecut.extract_frames_from_video(video_path, frame_dir, threshold=threshold,
+                                       device=str(embedding_service.device))
+    if not any(f.endswith(IMAGE_EXT) for f in os.listdir(frame_dir)):
+        raise RuntimeError(f"no scene cut found in {video_path} at threshold {threshold}: no key-frame to index")
+    embeddings_file = embedding_service.extract_and_save_embeddings_from_folder(frame_dir, model_name, video_name)
+    metadata_file = metadata_builder(frame_dir, os.path.join(ps.metadata_dir, f"{video_name}_metadata.json"),
+                                     video_path)
+    ps.add_video_mapping(video_name, metadata_file, embeddings_file, video_path, frame_dir)
+    ps.video_data_mapping[video_name]["embedding_model"] = model_name
+    ps.save_video_data_mapping()
+    return ps.video_data_mapping[video_name]
+
+
 def initialize_services(base_dir, metadata_dir, embedding_dir, finetuned_model_path=None, **embedding_kwargs):
     """services/__init__.py:11-64 for the services on this path (no SearchService / visualisation)."""
     path_service = PathService(base_dir, metadata_dir, embedding_dir)

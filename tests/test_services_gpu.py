@@ -294,3 +294,42 @@ def test_finetuned_checkpoint_switch(tmp_path, cuda, full_sd):
     svc2 = services.EmbeddingService(cs, ps, services.DataService(ps, cs), "cuda",
                                      load_kwargs=dict(state_dict=full_sd, max_batch=64), checkpoint_path=path)
     assert svc2.finetuned_model is not None and svc2.set_active_model("finetuned") is True
+
+
+def test_ingest_video_end_to_end(tmp_path, cuda, full_sd):
+    """The processing half of /api/upload-video (app.py:636-659): video file -> scene-cut key-frames on the GPU ->
+    embeddings -> metadata -> video_mapping.json; the new video is then searchable by one of its own key-frames."""
+    cv2 = pytest.importorskip("cv2")
+    from oracle import scenecut_oracle as sco
+    services = importlib.import_module(PKG + ".services")
+    clip = sco.synthetic_clip(75, h=96, w=128, cuts=(20, 41, 60), seed=12)
+    video = str(tmp_path / "demo.avi")
+    wr = cv2.VideoWriter(video, cv2.VideoWriter_fourcc(*"MJPG"), 25.0, (128, 96))
+    if not wr.isOpened():
+        pytest.skip("no MJPG writer in this cv2 build")
+    for f in clip:
+        wr.write(f)
+    wr.release()
+    svc, ps = _site(tmp_path, full_sd, {})
+    entry = services.ingest_video(svc, video, threshold=20.0)
+    assert set(entry) == {"metadata_file", "embeddings_file", "video_path", "frames_dir", "embedding_model"}
+    frames = sorted(os.listdir(entry["frames_dir"]))
+    assert frames == sorted(["10.jpg", "30.jpg", "50.jpg", "67.jpg"])       # middle frames of the 4 scenes
+    emb = np.load(entry["embeddings_file"])
+    assert emb.shape == (4, 512) and np.allclose(np.linalg.norm(emb, axis=-1), 1.0, atol=2e-3)
+    meta = json.load(open(entry["metadata_file"]))
+    assert [os.path.basename(m["filepath"]) for m in meta] == frames and meta[0]["frameidx"] == 10
+    assert meta[0]["video"] == video and meta[0]["object_detections"] == {"detections": []}
+    mapping = json.load(open(os.path.join(ps.metadata_dir, "video_mapping.json")))
+    assert mapping["demo"]["embeddings_file"] == entry["embeddings_file"]
+    # searchable: each key-frame finds itself first
+    for row, name in enumerate(frames):
+        top = svc.search_top_frames_by_image(emb[row:row + 1].astype(np.float32), 2, "demo")
+        assert top[0] == name
+    with pytest.raises(RuntimeError):   # a still clip has no cut -> no key-frame
+        still = str(tmp_path / "still.avi")
+        wr = cv2.VideoWriter(still, cv2.VideoWriter_fourcc(*"MJPG"), 25.0, (128, 96))
+        for _ in range(20):
+            wr.write(clip[0])
+        wr.release()
+        services.ingest_video(svc, still, threshold=20.0)
