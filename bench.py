@@ -166,6 +166,37 @@ def bench_encode_other(pkg, dev, name, batch, steps, warmup, peaks):
             "whole_step_frac": round(tf / peaks["tf_sustained"], 4), "achieved_tflops": round(tf, 1)}
 
 
+def bench_scenecut(pkg, dev, peaks, frames_n=256, steps=10, warmup=3):
+    """Secondary line: scene-cut scoring of 1280x720 frames resident in HBM (707 MB > L2)."""
+    import importlib
+
+    import torch
+    scenecut = importlib.import_module(pkg.__name__ + ".scenecut")
+    H, W = 720, 1280
+    g = torch.Generator(device=dev).manual_seed(11)
+    frames = torch.randint(0, 256, (frames_n, H, W, 3), dtype=torch.uint8, device=dev, generator=g)
+    det = scenecut.ContentDetector(device=dev)
+    for _ in range(warmup):
+        det.delta_sums(frames)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(steps):
+        det.delta_sums(frames)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    gbs = frames_n * H * W * 3 / (ms * 1e-3) / 1e9
+    return {"metric": "frames/s scene-cut scoring (HSV frame difference)", "unit": "frames/s",
+            "value": round(frames_n / ms * 1e3, 1), "ms_per_step": round(ms, 4), "steps": steps, "warmup": warmup,
+            "n_gpus": 1, "dtype": "u8/int32",
+            "config": {"workload": f"{frames_n} consecutive 1280x720 BGR frames, device-resident, per-pair |dH|,|dS|,|dV| sums"},
+            "roofline": {"bound": "hbm", "achieved": round(gbs, 1), "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                         "frac": round(gbs / peaks["hbm_gbs"], 4), "traffic": None,
+                         "note": "algorithmic bytes = every frame once (3 B per pixel); the kernel is bound by the "
+                                 "integer pipe on the exact OpenCV HSV arithmetic (profiles/r01_e_ncu_scenecut.txt)"}}
+
+
 # ----------------------------------------------------------------------------------------------- encode (ours)
 def bench_encode(pkg, dev, rank, world, steps, warmup, batch, peaks):
     import torch
@@ -504,6 +535,7 @@ def main():
     if rank == 0 and world == 1 and args.workload == "both":
         # BASELINE config 5's tower (ViT-L/14, 768-d) as a secondary line: 8 steps of 128 frames, about one second
         line["vit_l14"] = bench_encode_other(pkg, dev, "ViT-L/14", 128, 8, 3, peaks)
+        line["scenecut"] = bench_scenecut(pkg, dev, peaks)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         fps, threads = cpu_encode(vo, n_batches=8)
         qps = cpu_search(so, 1_000_000, 4, args.k)

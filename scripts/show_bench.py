@@ -13,3 +13,9 @@ if s:
 v = d.get("vit_l14")
 if v:
     print("vit_l14", v["value"], "frames/s", v["ms_per_step"], "ms | whole-step frac", v["whole_step_frac"])
+c = d.get("scenecut")
+if c:
+    print("scenecut", c["value"], "frames/s", c["ms_per_step"], "ms | hbm frac", c["roofline"]["frac"])
+dt = r.get("device_timer")
+if dt:
+    print("gemm device timer:", dt["avg_launch_ms"], "ms/launch, frac", dt["frac"])
