@@ -93,13 +93,9 @@ scene_delta_kernel(const uint8_t* __restrict__ frames, int H, int W, int bgr, in
 
 // Aligned full-resolution path: a thread keeps its 4-pixel groups and walks them through kChunk consecutive frame
 // pairs, so every frame is read once and converted to HSV once per chunk (the pair kernel converts each frame twice);
-// the HSV of the previous frame stays packed in registers (h | s << 8 | v << 16).  grid (x, ceil(pairs / kChunk)).
+// the HSV of the previous frame stays packed in registers (one word per channel for the 4 pixels).  grid (x, ceil(pairs / kChunk)).
 constexpr int kChunk = 8;
 
-__device__ __forceinline__ uint32_t hsv_packed(int c0, int c1, int c2, int bgr, const int* sdiv, const int* hdiv) {
-  const Hsv p = hsv_u8(c0, c1, c2, bgr, sdiv, hdiv);
-  return static_cast<uint32_t>(p.h) | (static_cast<uint32_t>(p.s) << 8) | (static_cast<uint32_t>(p.v) << 16);
-}
 struct Words3 {
   uint32_t a0, a1, a2;  // 4 pixels = 12 bytes
 };
@@ -110,14 +106,19 @@ __device__ __forceinline__ Words3 load_group(const uint32_t* w, int gi) {
   r.a2 = __ldg(w + 3 * gi + 2);
   return r;
 }
-__device__ __forceinline__ void hsv_group(const Words3& w, int bgr, const int* sdiv, const int* hdiv, uint32_t (&o)[4]) {
-  o[0] = hsv_packed(w.a0 & 255, (w.a0 >> 8) & 255, (w.a0 >> 16) & 255, bgr, sdiv, hdiv);
-  o[1] = hsv_packed(w.a0 >> 24, w.a1 & 255, (w.a1 >> 8) & 255, bgr, sdiv, hdiv);
-  o[2] = hsv_packed((w.a1 >> 16) & 255, w.a1 >> 24, w.a2 & 255, bgr, sdiv, hdiv);
-  o[3] = hsv_packed((w.a2 >> 8) & 255, (w.a2 >> 16) & 255, w.a2 >> 24, bgr, sdiv, hdiv);
+// 4 pixels -> three words, one per channel (byte k = pixel k), so that one vabsdiff4.add per channel sums the four
+// differences; the packing multiplies run on the FMA pipe, which the conversion leaves idle
+__device__ __forceinline__ void hsv_group(const Words3& w, int bgr, const int* sdiv, const int* hdiv, uint32_t (&o)[3]) {
+  const Hsv p0 = hsv_u8(w.a0 & 255, (w.a0 >> 8) & 255, (w.a0 >> 16) & 255, bgr, sdiv, hdiv);
+  const Hsv p1 = hsv_u8(w.a0 >> 24, w.a1 & 255, (w.a1 >> 8) & 255, bgr, sdiv, hdiv);
+  const Hsv p2 = hsv_u8((w.a1 >> 16) & 255, w.a1 >> 24, w.a2 & 255, bgr, sdiv, hdiv);
+  const Hsv p3 = hsv_u8((w.a2 >> 8) & 255, (w.a2 >> 16) & 255, w.a2 >> 24, bgr, sdiv, hdiv);
+  o[0] = p0.h + p1.h * 256u + p2.h * 65536u + p3.h * 16777216u;
+  o[1] = p0.s + p1.s * 256u + p2.s * 65536u + p3.s * 16777216u;
+  o[2] = p0.v + p1.v * 256u + p2.v * 65536u + p3.v * 16777216u;
 }
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 4)
 scene_walk_kernel(const uint8_t* __restrict__ frames, int H, int W, int pairs, int bgr, const int* __restrict__ sdiv_g,
                   const int* __restrict__ hdiv_g, unsigned long long* __restrict__ sums) {
   __shared__ int sdiv[256], hdiv[256];
@@ -134,7 +135,7 @@ scene_walk_kernel(const uint8_t* __restrict__ frames, int H, int W, int pairs, i
 #pragma unroll
   for (int t = 0; t < kChunk; ++t) acc[t][0] = acc[t][1] = acc[t][2] = 0;
   for (int gi = blockIdx.x * blockDim.x + threadIdx.x; gi < groups; gi += gridDim.x * blockDim.x) {
-    uint32_t prev[4], cur[4];
+    uint32_t prev[3], cur[3];
     hsv_group(load_group(base, gi), bgr, sdiv, hdiv, prev);
     Words3 nxt = load_group(base + frame_words, gi);  // nt >= 1; the loads run one frame ahead of the arithmetic
 #pragma unroll
@@ -144,12 +145,9 @@ scene_walk_kernel(const uint8_t* __restrict__ frames, int H, int W, int pairs, i
         if (t + 1 < nt) nxt = load_group(base + (t + 2) * frame_words, gi);
         hsv_group(w, bgr, sdiv, hdiv, cur);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const uint32_t d = __vabsdiffu4(prev[k], cur[k]);  // per-byte |dh|, |ds|, |dv|
-          acc[t][0] += d & 255;
-          acc[t][1] += (d >> 8) & 255;
-          acc[t][2] += d >> 16;
-          prev[k] = cur[k];
+        for (int c = 0; c < 3; ++c) {
+          acc[t][c] += __vsadu4(prev[c], cur[c]);  // sum over the 4 pixels of |d| of this channel
+          prev[c] = cur[c];
         }
       }
     }
