@@ -167,3 +167,25 @@ def test_threaded_decode_is_ordered_bounded_and_identical(services, tmp_path):
         gen.close()
     finally:
         Image.open = real_open
+
+
+def test_frame_metadata_items_layout(services, tmp_path):
+    """Stand-in for process_images_in_folder (JSON_sample_DOC.py:74-84, :90): same keys, sorted frame order (= the row
+    order of the embedding file), frameidx from the digits of the file name."""
+    from PIL import Image
+    folder = tmp_path / "frames"
+    folder.mkdir()
+    for name in ("300.jpg", "7.jpg", "1061.jpg", "cover.png", "notes.txt"):
+        if name.endswith(".txt"):
+            (folder / name).write_text("x")
+        else:
+            Image.new("RGB", (32, 18), (10, 20, 30)).save(folder / name)
+    out = services.frame_metadata_items(str(folder), str(tmp_path / "meta" / "v_metadata.json"), "/videos/v.mp4")
+    items = json.load(open(out))
+    assert [i["frameid"] for i in items] == sorted(["300.jpg", "7.jpg", "1061.jpg", "cover.png"])
+    first = items[0]
+    assert set(first) == {"id", "media_type", "filepath", "tags", "metadata", "video", "frameid", "text_detections",
+                          "object_detections", "frameidx"}
+    assert first["metadata"] == {"width": 32, "height": 18} and first["video"] == "/videos/v.mp4"
+    assert {i["frameid"]: i["frameidx"] for i in items} == {"1061.jpg": 1061, "300.jpg": 300, "7.jpg": 7,
+                                                           "cover.png": None}
