@@ -20,3 +20,5 @@ python bench.py --impl reference --steps 2 --warmup 1 > $O/r01_e_bench_reference
 python scripts/torch_eager_baseline.py > $O/r01_e_torch_eager.json 2> $O/r01_e_torch_eager.err
 python scripts/graph_probe.py > $O/r01_e_small_batch.txt 2>&1
 EVR_NO_GRAPH=1 python scripts/graph_probe.py >> $O/r01_e_small_batch.txt 2>&1
+python scripts/scenecut_probe.py > $O/plain_scene.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:scene_walk -s 2 -c 1 -o $O/r01_e_prof_scene -f python scripts/scenecut_probe.py > $O/ncu_scene.log 2>&1
