@@ -19,8 +19,9 @@ import time
 import numpy as np
 import torch
 
-from collections import deque
+from collections import OrderedDict, deque
 from concurrent.futures import ThreadPoolExecutor
+from pathlib import Path
 
 from . import clip as _clip
 from .preprocess import GpuPreprocess
@@ -132,6 +133,8 @@ class DataService:
 
     def __init__(self, path_service, cache_service):
         self.path_service, self.cache_service = path_service, cache_service
+        self._fps = {}
+        self.frames_mapping = self.load_frames_mapping_from_json()   # data_service.py:22
 
     def load_frames_from_json(self, video_name=None):
         json_path = self.path_service.get_metadata_path(video_name)
@@ -148,6 +151,103 @@ class DataService:
         except Exception as e:  # the reference swallows and returns []
             print(f"Error loading frames from JSON: {e}, path: {json_path}")
             return []
+
+    def load_frames_mapping_from_json(self, video_name=None):
+        """data_service.py:57-79 -- {frame file name: full path}; {} on any error."""
+        json_path = os.path.normpath(self.path_service.get_metadata_path(video_name))
+        try:
+            with open(json_path, "r", encoding="utf-8") as f:
+                return {Path(sample["filepath"]).name: sample["filepath"] for sample in json.load(f)}
+        except Exception as e:
+            print(f"Error loading frames mapping from JSON: {e}, path: {json_path}")
+            return {}
+
+    def load_json_data(self, video_name=None):
+        """data_service.py:127-145 -- the metadata records of a video (file order); [] on any error."""
+        json_path = self.path_service.get_metadata_path(video_name)
+        try:
+            with open(json_path, "r", encoding="utf-8") as f:
+                return json.load(f)
+        except Exception as e:
+            print(f"Error loading data from JSON: {e}, path: {json_path}")
+            return []
+
+    def _video_fps(self, video_path):
+        """fps used for `timestamp`: the file's own when it can be opened, else 25.0 (data_service.py:217-229).
+        Probed once per (path, mtime) instead of on every event."""
+        if not video_path or not os.path.exists(video_path):
+            return 25.0
+        key = (video_path, os.path.getmtime(video_path))
+        fps = self._fps.get(key)
+        if fps is None:
+            fps = 25.0
+            try:
+                import cv2
+                cap = cv2.VideoCapture(video_path)
+                if cap.isOpened():
+                    actual = cap.get(cv2.CAP_PROP_FPS)
+                    if actual > 0:
+                        fps = actual
+                    cap.release()
+            except Exception as e:
+                print(f"Error getting video fps: {e}")
+            self._fps[key] = fps
+        return fps
+
+    def get_video_duration(self, video_path):
+        try:
+            import cv2
+            cap = cv2.VideoCapture(video_path)
+            if not cap.isOpened():
+                return 0
+            fps, frames = cap.get(cv2.CAP_PROP_FPS), int(cap.get(cv2.CAP_PROP_FRAME_COUNT))
+            cap.release()
+            return round(frames / fps if fps > 0 else 0)
+        except Exception:
+            return 0
+
+    def format_event_for_frontend(self, frame_data):
+        """data_service.py:147-251 -- the event dict the UI receives.  `confidence` starts at 0.7, becomes the best OCR
+        confidence when there is OCR text, the best object confidence when that is higher, and the CLIP similarity
+        when that is higher still; `detection_type` names the winner."""
+        video_path = frame_data.get('video', '')
+        video_id = f"video-{Path(video_path).stem}" if video_path else 'unknown'
+        category, description, detection_type = "Unknown", "Event detected", "unknown"
+        confidence, text_confidence, object_confidence = 0.7, 0.0, 0.0
+
+        texts = (frame_data.get('text_detections') or {}).get('detections') or []
+        if texts:
+            best = max(texts, key=lambda d: d.get('confidence', 0))
+            label = best.get('label')
+            category = label.split(' ')[0] if label else "Unknown"
+            text_confidence = _pyfloat(best.get('confidence', 0.7))
+            description = best.get('label', 'Event detected')
+            detection_type, confidence = "text", text_confidence
+
+        objects = (frame_data.get('object_detections') or {}).get('detections') or []
+        if objects:
+            best = max(objects, key=lambda d: d.get('confidence', 0))
+            object_confidence = _pyfloat(best.get('confidence', 0.5))
+            if object_confidence > text_confidence:
+                category = best.get('label', 'Unknown')
+                description = f"Object detected: {category}"
+                detection_type, confidence = "object", object_confidence
+
+        clip_similarity = frame_data.get('clip_similarity', 0.0)
+        clip_similarity = 0.0 if clip_similarity is None else _pyfloat(clip_similarity)
+        if clip_similarity > confidence:
+            detection_type, confidence = "clip", clip_similarity
+
+        frame_idx = frame_data.get('frameidx', 0)
+        return {"id": f"event-{frame_idx}", "videoId": video_id, "title": f"Event at frame {frame_idx}",
+                "description": description, "timestamp": _pyfloat(frame_idx / self._video_fps(video_path)),
+                "duration": 5, "category": category, "confidence": confidence, "text_confidence": text_confidence,
+                "object_confidence": object_confidence, "clip_similarity": clip_similarity,
+                "detection_type": detection_type, "thumbnailUrl": frame_data.get('filepath')}
+
+
+def _pyfloat(x):
+    return float(x) if type(x).__module__ == "numpy" else x
 
 
 def decode_frames(paths, workers=None, window=None):
@@ -208,6 +308,7 @@ class EmbeddingService:
         self.active_model = "original"
         self.checkpoint_path = checkpoint_path
         self._stores = {}              # embeddings_path -> (mtime, FrameStore, source dtype)
+        self._scan_scores = OrderedDict()  # (model, query, video) -> (FrameStore, {frame name: cosine}) of past scans
         self._lock = threading.RLock()  # the Flask dev server is threaded (app.py:968); the reference holds no locks
         if checkpoint_path and os.path.exists(checkpoint_path):
             try:
@@ -310,12 +411,24 @@ class EmbeddingService:
 
     # ---- re-score (a11) ---------------------------------------------------------------------------
     def extract_query_confidence(self, frame_path, query, video_name=None):
-        """cosine(frame row, text features) as a python float; 0.0 on a miss or any error (:219-282)."""
+        """cosine(frame row, text features) as a python float; 0.0 on a miss or any error (:219-282).
+
+        The strategies call this once per candidate right after `search_top_frames(query, top_k*3, video)`
+        (query_strategies.py:55, :100): the scan has already produced exactly this dot product, so it is answered from
+        the scan's own (frame, score) pairs (SURVEY.md 8g "search_top_frames drops scores") and only a frame the scan
+        did not return costs a kernel (`evr_rescore`)."""
         try:
             text_features = self.get_text_features(query, video_name)
             entry, _ = self._frame_store(video_name)
             if entry is None:
                 return 0.0
+            known = self._scan_scores.get((self.active_model, query, video_name or 'default'))
+            if known is not None and known[0] is entry[1]:
+                score = known[1].get(frame_path)
+                if score is None:
+                    score = known[1].get(os.path.basename(frame_path))
+                if score is not None:
+                    return score
             index = self._row_index(video_name).get(frame_path)
             if index is None:
                 index = self._row_index(video_name).get(os.path.basename(frame_path))
@@ -344,9 +457,8 @@ class EmbeddingService:
             return table
 
     # ---- the scan (a9, a10) -----------------------------------------------------------------------
-    def search_with_scores(self, features, top_k, video_name=None):
-        """[(frame name, cosine)] in descending score: the pairs the reference builds at :330-333 before it drops
-        the scores.  `features` [1, D] / [D] unit-norm query."""
+    def _scan(self, features, top_k, video_name=None):
+        """-> [(frame name, cosine, store row)] best first: the fused scan (evr_topk_search) over the video's store."""
         entry, _ = self._frame_store(video_name)
         if entry is None:
             return []
@@ -355,7 +467,12 @@ class EmbeddingService:
         scores, idx = store.search(q, min(int(top_k), store.N))
         scores, idx = scores[0].cpu().numpy(), idx[0].cpu().numpy()
         frames = self._frames(video_name)
-        return [(frames[int(i)], float(s)) for i, s in zip(idx, scores)]
+        return [(frames[int(i)], float(s), int(i)) for i, s in zip(idx, scores)]
+
+    def search_with_scores(self, features, top_k, video_name=None):
+        """[(frame name, cosine)] in descending score: the pairs the reference builds at :330-333 before it drops
+        the scores.  `features` [1, D] / [D] unit-norm query."""
+        return [(f, s) for f, s, _ in self._scan(features, top_k, video_name)]
 
     def search_top_frames(self, query, top_k, video_name=None):
         """list of frame file names, best first; [] on any error; memoised like the reference (:284-344)."""
@@ -365,13 +482,36 @@ class EmbeddingService:
             if cached is not None:
                 return cached
             text_features = self.get_text_features(query, video_name)
-            top_frames = [f for f, _ in self.search_with_scores(text_features, top_k, video_name)]
+            hits = self._scan(text_features, top_k, video_name)
+            self._remember_scores(query, video_name, hits)
+            top_frames = [f for f, _, _ in hits]
             if top_frames or self._frame_store(video_name)[0] is not None:
                 self.cache_service.set_search_results(cache_key, video_name, top_frames)
             return top_frames
         except Exception as e:
             print(f"Error in search_top_frames: {e}")
             return []
+
+    def _remember_scores(self, query, video_name, hits, keep=256):
+        """(model, query, video) -> (store, {frame: cosine}) for the candidates of the last scans.  Only the first row
+        carrying a frame name is recorded, because that is the row `frames.index(name)` scores (:264).  Bounded: the
+        oldest of `keep` queries is dropped."""
+        entry, _ = self._frame_store(video_name)
+        if entry is None or not hits:
+            return
+        first_row = self._row_index(video_name)
+        key = (self.active_model, query, video_name or 'default')
+        with self._lock:
+            old = self._scan_scores.get(key)
+            table = dict(old[1]) if old is not None and old[0] is entry[1] else {}
+            for name, score, row in hits:
+                if first_row.get(name) == row:
+                    table[name] = score
+                    table.setdefault(os.path.basename(name), score)
+            self._scan_scores[key] = (entry[1], table)
+            self._scan_scores.move_to_end(key)
+            while len(self._scan_scores) > keep:
+                self._scan_scores.popitem(last=False)
 
     def search_top_frames_by_image(self, image_features, top_k, video_name=None):
         """Same scan with a given [1, D] query vector, no result cache (:346-392)."""
@@ -509,14 +649,147 @@ class _FinetunedImageEncoder:
         return self
 
 
+class SearchService:
+    """Drop-in for the part of Backend/services/search_service.py that `app.py` reaches on this path (SURVEY.md 8a
+    row a15): same constructor positionals, `search_by_image(image_url, adaptive_threshold, top_k, video_name=None,
+    preprocess=None)` (:611-705), `search_semantic_with_clip` (:121-177), `search_frames_by_keyword` (:25-58, the
+    callback the keyword strategies take), `sort_by_confidence` (:605-609).  The other `search_by_*` methods of the
+    reference class duplicate query_strategies.py and are not called by `app.py`; they forward
+    to the strategy functions here."""
+
+    def __init__(self, embedding_service, data_service, path_service, cache_service):
+        self.embedding_service, self.data_service = embedding_service, data_service
+        self.path_service, self.cache_service = path_service, cache_service
+
+    # ---- OCR keyword lookup (metadata only; no arithmetic) ----------------------------------------
+    def search_frames_by_keyword(self, keyword, top_k, video_name=None):
+        """frame ids whose OCR text contains the keyword (accent-insensitive), ranked by the confidence of the FIRST
+        matching detection of each frame (the reference `break`s at the first hit, :49-55), best `top_k`."""
+        from ._unaccent import unidecode
+        needle = unidecode(keyword.lower())
+        matches = []
+        for record in self.data_service.load_json_data(video_name):
+            for det in record.get("text_detections", {}).get("detections", []):
+                label = det.get("label", "")
+                if label and needle in unidecode(label.lower()):
+                    matches.append((record.get("frameid", ""), det.get("confidence", 0)))
+                    break
+        matches.sort(key=lambda m: m[1], reverse=True)
+        return [frameid for frameid, _ in matches[:top_k]]
+
+    # ---- CLIP text search with a threshold ---------------------------------------------------------
+    def search_semantic_with_clip(self, query, adaptive_threshold, top_k, video_name=None):
+        """:121-177 -- `query_by_text_with_adaptive_threshold` without the text preprocessing step, over this
+        service's own embedding / data services."""
+        try:
+            svc = self.embedding_service
+            by_frameidx = {}
+            for item in self.data_service.load_json_data(video_name):
+                by_frameidx.setdefault(item.get('frameidx'), item)
+            results = []
+            for frame_name in svc.search_top_frames(query, top_k * 3, video_name):
+                try:
+                    record = by_frameidx.get(int(Path(frame_name).stem))
+                    if not record:
+                        continue
+                    confidence = svc.extract_query_confidence(frame_name, query, video_name)
+                    if confidence >= adaptive_threshold:
+                        event = self.data_service.format_event_for_frontend(dict(record, clip_similarity=confidence))
+                        event["clip_similarity"] = confidence
+                        results.append(event)
+                except Exception as e:
+                    print(f"Error processing frame {frame_name}: {e}")
+            results.sort(key=lambda x: x.get("clip_similarity", 0), reverse=True)
+            return results[:top_k]
+        except Exception as e:
+            print(f"Error in semantic search: {e}")
+            return []
+
+    # ---- image query -------------------------------------------------------------------------------
+    @staticmethod
+    def _open_image(image_url):
+        import base64
+        from io import BytesIO
+        from PIL import Image
+        if hasattr(image_url, "convert"):
+            return image_url.convert('RGB')
+        if image_url.startswith(('http://', 'https://')):
+            import requests  # the reference downloads the URL (:633-636); offline boxes raise here -> []
+            return Image.open(BytesIO(requests.get(image_url, timeout=10).content)).convert('RGB')
+        if image_url.startswith('data:image'):
+            # the reference hands the base64 TEXT to PIL (:639-640), which can never decode; the payload is decoded here
+            return Image.open(BytesIO(base64.b64decode(image_url.split(',')[1]))).convert('RGB')
+        return Image.open(image_url).convert('RGB')
+
+    def search_by_image(self, image_url, adaptive_threshold, top_k, video_name=None, preprocess=None,
+                        format_event_for_frontend=None):
+        """:611-705 -- encode the query image, scan with `top_k * 3`, keep candidates whose cosine passes
+        `adaptive_threshold`, best `top_k` events (`confidence` = `clip_similarity` = the cosine).
+
+        Difference from the reference: a candidate's similarity is the scan's own score -- the dot
+        product of its store row with the query -- instead of re-embedding the frame through
+        `extract_image_embedding(<basename>)` (:679), which fails outside the frames directory and silently drops the
+        candidate, and costs up to 3 top_k extra tower passes when it does not."""
+        try:
+            svc = self.embedding_service
+            fmt = format_event_for_frontend or self.data_service.format_event_for_frontend
+            preprocess = preprocess if preprocess is not None else svc.preprocess
+            image = preprocess(self._open_image(image_url)).unsqueeze(0).to(svc.device)
+            with torch.no_grad():
+                if svc.get_active_model_name() == "finetuned" and svc.finetuned_model is not None:
+                    feats = svc.finetuned_model(image)
+                else:
+                    feats = svc.original_model.encode_image(image)
+                feats = feats.float()
+                feats = (feats / feats.norm(dim=-1, keepdim=True)).cpu().numpy()
+            by_frameidx = {}
+            for item in self.data_service.load_json_data(video_name):
+                by_frameidx.setdefault(item.get('frameidx'), item)
+            results = []
+            for frame_name, similarity in svc.search_with_scores(feats, top_k * 3, video_name):
+                try:
+                    record = by_frameidx.get(int(Path(frame_name).stem))
+                    if record and similarity >= adaptive_threshold:
+                        event = fmt(dict(record, clip_similarity=float(similarity)))
+                        event["clip_similarity"] = float(similarity)
+                        event["confidence"] = float(similarity)
+                        results.append(event)
+                except Exception as e:
+                    print(f"Error processing frame {frame_name}: {e}")
+            results.sort(key=lambda x: x.get("clip_similarity", 0), reverse=True)
+            return results[:top_k]
+        except Exception as e:
+            print(f"Error in image search: {e}")
+            return []
+
+    # ---- the reference class's duplicates of the strategies ---------------------------------------
+    def _strategy_args(self):
+        return dict(video_data_mapping=getattr(self.path_service, "video_data_mapping", {}))
+
+    def search_by_keyword(self, query, adaptive_threshold, top_k, video_name=None):
+        from . import query_strategies as qs
+        return qs.query_by_keyword(query, adaptive_threshold, top_k, self.search_frames_by_keyword,
+                                   self.data_service.format_event_for_frontend, video_name=video_name,
+                                   **self._strategy_args())
+
+    def search_by_object(self, query, adaptive_threshold, top_k, video_name=None):
+        from . import query_strategies as qs
+        return qs.query_by_object(query, adaptive_threshold, top_k, self.data_service.format_event_for_frontend,
+                                  video_name=video_name, **self._strategy_args())
+
+    def sort_by_confidence(self, results):
+        return sorted(results, key=lambda x: x.get("confidence", 0), reverse=True) if results else []
+
+
 def frame_metadata_items(folder_path, output_json_path, path_video):
     """Detector-free stand-in for `process_images_in_folder(folder_path, output_json_path, path_video)`
     (JSON_sample_DOC.py:90): the same item layout (:74-84) with empty OCR / object lists -- EasyOCR and YOLO are outside
-    this path -- written in sorted frame order so that item i describes embedding row i."""
+    this path -- written in sorted frame order with the ingest's own (case-sensitive, embedding_service.py:452) file filter, so that
+    item i describes embedding row i."""
     import uuid
     from PIL import Image
     items = []
-    for name in sorted(f for f in os.listdir(folder_path) if f.lower().endswith(('.png', '.jpg', '.jpeg'))):
+    for name in sorted(f for f in os.listdir(folder_path) if f.endswith(IMAGE_EXT)):   # the rows of the ingest, exactly
         path = os.path.join(folder_path, name)
         with Image.open(path) as im:
             width, height = im.size
@@ -549,6 +822,11 @@ def ingest_video(embedding_service, video_path, video_name=None, model_name="ori
     embeddings_file = embedding_service.extract_and_save_embeddings_from_folder(frame_dir, model_name, video_name)
     metadata_file = metadata_builder(frame_dir, os.path.join(ps.metadata_dir, f"{video_name}_metadata.json"),
                                      video_path)
+    with open(metadata_file, "r", encoding="utf-8") as f:
+        n_items = len(json.load(f))
+    n_rows = np.load(embeddings_file, mmap_mode="r").shape[0]
+    if n_items != n_rows:  # row i <-> item i is the identity every search result rests on
+        raise RuntimeError(f"{video_name}: {n_rows} embedding rows but {n_items} metadata items")
     ps.add_video_mapping(video_name, metadata_file, embeddings_file, video_path, frame_dir)
     ps.video_data_mapping[video_name]["embedding_model"] = model_name
     ps.save_video_data_mapping()
@@ -556,12 +834,13 @@ def ingest_video(embedding_service, video_path, video_name=None, model_name="ori
 
 
 def initialize_services(base_dir, metadata_dir, embedding_dir, finetuned_model_path=None, **embedding_kwargs):
-    """services/__init__.py:11-64 for the services on this path (no SearchService / visualisation)."""
+    """services/__init__.py:11-64 for the services on this path (no visualisation service)."""
     path_service = PathService(base_dir, metadata_dir, embedding_dir)
     cache_service = CacheService()
     data_service = DataService(path_service, cache_service)
     embedding_service = EmbeddingService(cache_service, path_service, data_service, "cuda",
                                          checkpoint_path=finetuned_model_path, **embedding_kwargs)
+    search_service = SearchService(embedding_service, data_service, path_service, cache_service)
     return {'path_service': path_service, 'cache_service': cache_service, 'data_service': data_service,
-            'embedding_service': embedding_service, 'search_service': None, 'device': "cuda",
+            'embedding_service': embedding_service, 'search_service': search_service, 'device': "cuda",
             'services_loaded': True}
