@@ -42,6 +42,11 @@ SIGNATURES = {
     "evr_topk_search": (c_int, [c_void_p, c_int64, c_int, c_int64, c_void_p, c_int, c_int, c_void_p, c_void_p,
                                 c_void_p, c_size_t, c_void_p]),
     "evr_topk_merge": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "evr_topk_large_workspace_bytes": (c_int, [c_int64, c_int, c_int64, ctypes.POINTER(c_size_t)]),
+    "evr_topk_search_large": (c_int, [c_void_p, c_int64, c_int, c_int64, c_void_p, c_int, c_int64, c_void_p, c_void_p,
+                                      c_void_p, c_size_t, c_void_p]),
+    "evr_topk_merge_large": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_size_t,
+                                     c_void_p]),
     "evr_rescore": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     "evr_vit_create": (c_int, [ctypes.POINTER(VitCfg), ctypes.POINTER(c_void_p), c_int, c_int,
                                ctypes.POINTER(c_void_p)]),

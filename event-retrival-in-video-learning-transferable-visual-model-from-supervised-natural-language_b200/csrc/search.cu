@@ -102,6 +102,7 @@ struct ScanArgs {
   float* group_max;    // sample pass only (else nullptr): [q_pad][groups] max score of every 64-row group
   int groups;          // 64-row groups in the sample = N / 64
   int stages;          // depth of the store-row smem ring actually used (<= kScanStages; 2 at D = 768)
+  int tile_stride;     // sample pass: tile t of the launch reads store tile t * tile_stride (1 in the full scan)
 };
 
 // Warp-cooperative exact prune of one query's candidate list to its top-k.  All 32 lanes call with the
@@ -231,7 +232,8 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         int64_t t1 = t0 + args.tiles_per_slice;
         if (t1 > total_tiles) t1 = total_tiles;
         for (int64_t t = t0; t < t1; ++t) {
-          const int row = static_cast<int>(t * kRowTile) + static_cast<int>(rank) * kScanRowTile;  // this CTA's half
+          const int row = static_cast<int>(t * args.tile_stride * kRowTile) +
+                          static_cast<int>(rank) * kScanRowTile;  // this CTA's half of the (strided) tile
           for (int kb = 0; kb < num_kb; ++kb) {
             mbar_wait(&empty_bar[stage], phase ^ 1);
             if constexpr (CG == 2) {
@@ -639,6 +641,133 @@ topk_final_kernel(const float* __restrict__ scores, const IdxT* __restrict__ idx
   }
 }
 
+// ============================================================================ large k (k > kMaxFusedK)
+// The reference accepts any top_k (embedding_service.py:317-320 sorts all N scores).  Requests beyond the fused
+// kernel's list capacity take this two-step path: (1) all scores of a few queries are written out once,
+// `scores_rows_kernel`: a warp per store row, the row read once and dotted with up to 8 resident queries (HBM-bound,
+// N*D*2 bytes per chunk of 8 queries + N*4*QC written); (2) `topk_large_kernel`, one CTA per query: 8-pass radix
+// select of the k-th 64-bit key (score key << 32 | ~row: unique, ties broken by ascending row) straight over global
+// memory, compaction of the k winners, bitonic sort of them in a global scratch area.  Also the merge of gathered
+// per-shard lists when k > 1024 (element e of query q lives at ((e / kin) * q_stride + q) * kin + e % kin).
+constexpr int kLargeQChunk = 8;
+
+__global__ void __launch_bounds__(256)
+scores_rows_kernel(const __half* __restrict__ store, int64_t N, int D, const __half* __restrict__ queries, int QC,
+                   float* __restrict__ out /* [QC][N] */) {
+  extern __shared__ __align__(16) uint8_t qsm[];
+  __half2* q2 = reinterpret_cast<__half2*>(qsm);  // [QC][D/2]
+  const int half_d = D / 2;
+  for (int i = threadIdx.x; i < QC * half_d; i += blockDim.x)
+    q2[i] = reinterpret_cast<const __half2*>(queries)[i];
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int64_t row = static_cast<int64_t>(blockIdx.x) * 8 + warp; row < N; row += static_cast<int64_t>(gridDim.x) * 8) {
+    const __half2* x = reinterpret_cast<const __half2*>(store + row * D);
+    float acc[kLargeQChunk];
+#pragma unroll
+    for (int j = 0; j < kLargeQChunk; ++j) acc[j] = 0.f;
+    for (int i = lane; i < half_d; i += 32) {
+      const float2 a = __half22float2(x[i]);
+#pragma unroll
+      for (int j = 0; j < kLargeQChunk; ++j) {
+        if (j < QC) {
+          const float2 b = __half22float2(q2[j * half_d + i]);
+          acc[j] += a.x * b.x + a.y * b.y;
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < kLargeQChunk; ++j) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], o);
+    }
+    if (lane == 0) {
+      for (int j = 0; j < QC; ++j) out[static_cast<size_t>(j) * N + row] = acc[j];
+    }
+  }
+}
+
+__global__ void __launch_bounds__(1024)
+topk_large_kernel(const float* __restrict__ scores, const int64_t* __restrict__ idx /* nullptr: idx = position */,
+                  int P, int q_stride, int64_t kin, int64_t kout, int64_t row_offset,
+                  unsigned long long* __restrict__ scratch /* [gridDim.x][kp] */, int64_t kp,
+                  float* __restrict__ out_scores, int64_t* __restrict__ out_idx) {
+  __shared__ unsigned hist[256];
+  __shared__ unsigned long long s_prefix;
+  __shared__ long long s_remaining;
+  __shared__ unsigned long long s_count;
+  const int q = blockIdx.x, tid = threadIdx.x, nt = blockDim.x;
+  const int64_t n = static_cast<int64_t>(P) * kin;
+  unsigned long long* win = scratch + static_cast<size_t>(q) * kp;
+  auto key_at = [&](int64_t e) -> unsigned long long {
+    const int64_t p = e / kin, j = e - p * kin;
+    const size_t off = (static_cast<size_t>(p) * q_stride + q) * kin + j;
+    const uint32_t id = idx ? static_cast<uint32_t>(idx[off]) : static_cast<uint32_t>(j);
+    return (static_cast<unsigned long long>(float_to_key(__float_as_uint(scores[off]))) << 32) |
+           static_cast<uint32_t>(~id);
+  };
+  if (tid == 0) { s_prefix = 0ull; s_remaining = kout; s_count = 0ull; }
+  __syncthreads();
+  unsigned long long T = 0ull;
+  if (n > kout) {
+    unsigned long long himask = 0ull;
+    for (int shift = 56; shift >= 0; shift -= 8) {
+      if (tid < 256) hist[tid] = 0;
+      __syncthreads();
+      const unsigned long long prefix = s_prefix;
+      for (int64_t e = tid; e < n; e += nt) {
+        const unsigned long long key = key_at(e);
+        if ((key & himask) == prefix) atomicAdd(&hist[(key >> shift) & 255ull], 1u);
+      }
+      __syncthreads();
+      if (tid == 0) {
+        long long rem = s_remaining, acc = 0;
+        int b = 255;
+        for (; b > 0; --b) {
+          if (acc + static_cast<long long>(hist[b]) >= rem) break;
+          acc += hist[b];
+        }
+        s_remaining = rem - acc;
+        s_prefix = prefix | (static_cast<unsigned long long>(b) << shift);
+      }
+      himask |= 255ull << shift;
+      __syncthreads();
+    }
+    T = s_prefix;
+  }
+  for (int64_t i = tid; i < kp; i += nt) win[i] = 0ull;  // key 0 sorts last (score -inf / row -1 padding)
+  __syncthreads();
+  for (int64_t e = tid; e < n; e += nt) {
+    const unsigned long long key = key_at(e);
+    if (key >= T) {
+      const unsigned long long pos = atomicAdd(&s_count, 1ull);
+      if (pos < static_cast<unsigned long long>(kp)) win[pos] = key;
+    }
+  }
+  __syncthreads();
+  for (int64_t size = 2; size <= kp; size <<= 1) {
+    for (int64_t stride = size >> 1; stride > 0; stride >>= 1) {
+      for (int64_t i = tid; i < kp; i += nt) {
+        const int64_t j = i ^ stride;
+        if (j > i) {
+          const bool desc = (i & size) == 0;
+          const unsigned long long x = win[i], y = win[j];
+          if ((x < y) == desc) { win[i] = y; win[j] = x; }
+        }
+      }
+      __syncthreads();
+    }
+  }
+  for (int64_t i = tid; i < kout; i += nt) {
+    const unsigned long long key = win[i];
+    const uint32_t sbits = key_to_float_bits(static_cast<uint32_t>(key >> 32));
+    const bool pad = key == 0ull || sbits == kNegInfBits;
+    out_scores[static_cast<size_t>(q) * kout + i] = pad ? -INFINITY : __uint_as_float(sbits);
+    out_idx[static_cast<size_t>(q) * kout + i] =
+        pad ? -1 : static_cast<int64_t>(~static_cast<uint32_t>(key)) + row_offset;
+  }
+}
+
 // ============================================================================ re-score
 __global__ void __launch_bounds__(256)
 rescore_kernel(const __half* __restrict__ store, int64_t N, int D, const __half* __restrict__ query,
@@ -718,7 +847,7 @@ static void plan_core(int64_t N, int Q, int k, int sm_total, ScanCore* p) {
   p->grid = static_cast<int>(items < sms ? items : sms) * p->cg;
 }
 
-// Sample pass: the scan kernel runs over the first n0 rows recording only the maximum of every 64-row group; the
+// Sample pass: the scan kernel runs over n0 rows (whole tiles spread evenly over the store) recording only the maximum of every 64-row group; the
 // k-th largest group maximum of a query is a lower bound on its global k-th best score, so the full scan starts
 // with a pass rate of ~k/n0 instead of admitting (and pruning) everything until its own threshold settles.
 // n0 ~ the rows one SM sees at small query batch, <= 1/64 of larger stores: < 2 % of the scan.
@@ -827,18 +956,21 @@ extern "C" int evr_topk_workspace_bytes(int64_t N, int D, int Q, int k, size_t* 
   return 0;
 }
 
-static int run_scan(const ScanCore& c, const void* store, int64_t N, int D, const void* queries, int Q, int k,
-                    const float* init_thresh, int2* lists, int* counts, float* group_max, int groups,
-                    cudaStream_t s) {
+// N rows are scanned; the store itself holds N_store >= N rows and tile t of the launch reads store tile
+// t * tile_stride (the sample pass spreads its n0 rows evenly over the whole store, so a store laid out video by video
+// in temporal order still yields a representative threshold; tile_stride = 1 and N_store = N for the full scan).
+static int run_scan(const ScanCore& c, const void* store, int64_t N, int64_t N_store, int tile_stride, int D,
+                    const void* queries, int Q, int k, const float* init_thresh, int2* lists, int* counts,
+                    float* group_max, int groups, cudaStream_t s) {
   ScanArgs a{};
-  a.N = N; a.D = D; a.Q = Q; a.k = k;
+  a.N = N; a.D = D; a.Q = Q; a.k = k; a.tile_stride = tile_stride;
   a.num_qt = c.num_qt; a.num_slices = c.num_slices; a.tiles_per_slice = c.tiles_per_slice; a.q_pad = c.q_pad;
   a.cap = c.cap;
   a.init_thresh = init_thresh;
   a.lists = lists; a.counts = counts; a.group_max = group_max; a.groups = groups;
   CUtensorMap tq, ts;
   if (int r = make_tmap_2d_16b(&tq, queries, Q, D, static_cast<uint64_t>(D) * 2, kScanQTile, false)) return r;
-  if (int r = make_tmap_2d_16b(&ts, store, N, D, static_cast<uint64_t>(D) * 2, kScanRowTile, false)) return r;
+  if (int r = make_tmap_2d_16b(&ts, store, N_store, D, static_cast<uint64_t>(D) * 2, kScanRowTile, false)) return r;
   // the resident query tile takes 128 * D * 2 bytes; the ring gets what is left of the 227 KB (6 stages up to D = 512,
   // 2 at D = 768: ViT-L/14 stores scan correctly, with a shallower pipeline)
   int stages = (227 * 1024 - 1024 - 256 - kScanQTile * D * 2) / kScanStageBytes;
@@ -872,7 +1004,10 @@ extern "C" int evr_topk_search(const void* store, int64_t N, int D, int64_t row_
   float* thresh = reinterpret_cast<float*>(ws + p.lists_bytes + p.counts_bytes + p.gmax_bytes);
   const float* init = nullptr;
   if (p.n0 > 0) {
-    if (int r = run_scan(p.pre, store, p.n0, D, queries, Q, k, nullptr, nullptr, nullptr, gmax, p.groups, s)) return r;
+    const int rowtile = kScanRowTile * p.pre.cg;
+    const int64_t stride = (N / rowtile) / (p.n0 / rowtile);  // >= 4: n0 <= N / 4, whole tiles only
+    if (int r = run_scan(p.pre, store, p.n0, N, static_cast<int>(stride), D, queries, Q, k, nullptr, nullptr, nullptr,
+                         gmax, p.groups, s)) return r;
     {
       ProfScope ps(PF_FINAL, s);
       sample_kth_kernel<<<(Q + 7) / 8, 256, 0, s>>>(gmax, p.groups, Q, k, thresh);
@@ -880,7 +1015,7 @@ extern "C" int evr_topk_search(const void* store, int64_t N, int D, int64_t row_
     EVR_CHECK_LAUNCH();
     init = thresh;
   }
-  if (int r = run_scan(p.main, store, N, D, queries, Q, k, init, lists, counts, nullptr, 0, s)) return r;
+  if (int r = run_scan(p.main, store, N, N, 1, D, queries, Q, k, init, lists, counts, nullptr, 0, s)) return r;
   SelectArgs sa{};
   sa.lists = lists; sa.counts = counts;
   sa.P = p.main.num_slices; sa.q_pad = p.main.q_pad; sa.cap = p.main.cap; sa.k = k; sa.smem_cap = p.select_cap;
@@ -905,6 +1040,75 @@ extern "C" int evr_topk_merge(const float* scores, const int64_t* idx, int P, in
   EVR_REQUIRE(scores && idx && out_scores && out_idx, "evr_topk_merge: null pointer");
   EVR_REQUIRE(P >= 1 && Q >= 1 && k >= 1 && k <= 1024, "evr_topk_merge: bad shape P=%d Q=%d k=%d", P, Q, k);
   return launch_final<int64_t>(scores, idx, P, Q, Q, k, 0, out_scores, out_idx, static_cast<cudaStream_t>(stream));
+}
+
+static int64_t pow2_at_least(int64_t k) {
+  int64_t kp = 1;
+  while (kp < k) kp <<= 1;
+  return kp;
+}
+
+extern "C" int evr_topk_large_workspace_bytes(int64_t N, int Q, int64_t k, size_t* out_bytes) {
+  EVR_REQUIRE(out_bytes && N >= 1 && Q >= 1 && k >= 1, "evr_topk_large_workspace_bytes: bad arguments");
+  const int qc = Q < kLargeQChunk ? Q : kLargeQChunk;
+  *out_bytes = up256(static_cast<size_t>(qc) * N * sizeof(float)) +
+               up256(static_cast<size_t>(qc) * pow2_at_least(k < N ? k : N) * 8) + 256;
+  return 0;
+}
+
+extern "C" int evr_topk_search_large(const void* store, int64_t N, int D, int64_t row_offset, const void* queries,
+                                     int Q, int64_t k, float* out_scores, int64_t* out_idx, void* workspace,
+                                     size_t workspace_bytes, void* stream) {
+  EVR_REQUIRE(store && queries && out_scores && out_idx && workspace, "evr_topk_search_large: null pointer");
+  EVR_REQUIRE(N >= 1 && N < (int64_t(1) << 31) && D >= 2 && D % 2 == 0 && Q >= 1 && k >= 1 && k <= N,
+              "evr_topk_search_large: bad shape N=%lld D=%d Q=%d k=%lld (need 1 <= k <= N)", (long long)N, D, Q,
+              (long long)k);
+  size_t need = 0;
+  if (int r = evr_topk_large_workspace_bytes(N, Q, k, &need)) return r;
+  EVR_REQUIRE(workspace_bytes >= need, "evr_topk_search_large: workspace %zu < required %zu", workspace_bytes, need);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int qc_max = Q < kLargeQChunk ? Q : kLargeQChunk;
+  const int64_t kp = pow2_at_least(k);
+  uint8_t* ws = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~uintptr_t(255));
+  float* scores = reinterpret_cast<float*>(ws);
+  unsigned long long* scratch =
+      reinterpret_cast<unsigned long long*>(ws + up256(static_cast<size_t>(qc_max) * N * sizeof(float)));
+  const size_t qsm = static_cast<size_t>(kLargeQChunk) * D * 2;
+  EVR_REQUIRE(qsm <= 48 * 1024, "evr_topk_search_large: D=%d too wide", D);
+  const int64_t want_blocks = (N + 7) / 8;
+  const int blocks = static_cast<int>(want_blocks < 8LL * sm_count() ? want_blocks : 8LL * sm_count());
+  for (int q0 = 0; q0 < Q; q0 += kLargeQChunk) {
+    const int qc = Q - q0 < kLargeQChunk ? Q - q0 : kLargeQChunk;
+    {
+      ProfScope ps(PF_SCAN, s);
+      scores_rows_kernel<<<blocks, 256, qsm, s>>>(static_cast<const __half*>(store), N, D,
+                                                  static_cast<const __half*>(queries) + static_cast<size_t>(q0) * D, qc,
+                                                  scores);
+    }
+    EVR_CHECK_LAUNCH();
+    {
+      ProfScope ps(PF_FINAL, s);
+      topk_large_kernel<<<qc, 1024, 0, s>>>(scores, nullptr, 1, qc, N, k, row_offset, scratch, kp,
+                                            out_scores + static_cast<size_t>(q0) * k, out_idx + static_cast<size_t>(q0) * k);
+    }
+    EVR_CHECK_LAUNCH();
+  }
+  return 0;
+}
+
+extern "C" int evr_topk_merge_large(const float* scores, const int64_t* idx, int P, int Q, int64_t k, float* out_scores,
+                                    int64_t* out_idx, void* scratch, size_t scratch_bytes, void* stream) {
+  EVR_REQUIRE(scores && idx && out_scores && out_idx && scratch, "evr_topk_merge_large: null pointer");
+  EVR_REQUIRE(P >= 1 && Q >= 1 && k >= 1, "evr_topk_merge_large: bad shape P=%d Q=%d k=%lld", P, Q, (long long)k);
+  const int64_t kp = pow2_at_least(k);
+  EVR_REQUIRE(scratch_bytes >= static_cast<size_t>(Q) * kp * 8, "evr_topk_merge_large: scratch %zu < %zu",
+              scratch_bytes, static_cast<size_t>(Q) * kp * 8);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  ProfScope ps(PF_FINAL, s);
+  topk_large_kernel<<<Q, 1024, 0, s>>>(scores, idx, P, Q, k, k, 0, static_cast<unsigned long long*>(scratch), kp,
+                                       out_scores, out_idx);
+  EVR_CHECK_LAUNCH();
+  return 0;
 }
 
 extern "C" int evr_rescore(const void* store, int64_t N, int D, const void* query_fp16, const int64_t* rows, int R,

@@ -101,8 +101,21 @@ class FrameStore:
         return out_s, out_i
 
     def _search_large_k(self, q, k):
-        raise ValueError(f"top_k={k} exceeds the fused kernel's limit of {MAX_FUSED_K} (the reference UI asks for "
-                         "top_k*3 <= 300); split the request or lower top_k")
+        """k > 1024 (the reference takes any top_k: it sorts all N scores, embedding_service.py:317-320): a score pass
+        over the store per chunk of 8 queries + a per-query radix select / sort on the device
+        (evr_topk_search_large).  Same outputs and tie rule as the fused path."""
+        Q = q.shape[0]
+        out_s = torch.empty((Q, k), dtype=torch.float32, device=self.device)
+        out_i = torch.empty((Q, k), dtype=torch.int64, device=self.device)
+        need = ctypes.c_size_t(0)
+        check(lib.evr_topk_large_workspace_bytes(self.N, Q, k, ctypes.byref(need)), "evr_topk_large_workspace_bytes")
+        with torch.cuda.device(self.device), self._guard:
+            if self._ws is None or self._ws.numel() < need.value:
+                self._ws = torch.empty(need.value, dtype=torch.uint8, device=self.device)
+            check(lib.evr_topk_search_large(ptr(self.rows), self.N, self.D, self.row_offset, ptr(q), Q, k, ptr(out_s),
+                                            ptr(out_i), ptr(self._ws), self._ws.numel(), current_stream_ptr()),
+                  "evr_topk_search_large")
+        return out_s, out_i
 
     def rescore(self, query, rows):
         """cosine of `query` [D] with the given local rows -> fp32 [R] (embedding_service.py:274-279)."""
@@ -124,8 +137,14 @@ def merge_topk(scores, idx):
     out_s = torch.empty((Q, k), dtype=torch.float32, device=scores.device)
     out_i = torch.empty((Q, k), dtype=torch.int64, device=scores.device)
     with torch.cuda.device(scores.device):
-        check(lib.evr_topk_merge(ptr(scores), ptr(idx), P, Q, k, ptr(out_s), ptr(out_i), current_stream_ptr()),
-              "evr_topk_merge")
+        if k <= MAX_FUSED_K:
+            check(lib.evr_topk_merge(ptr(scores), ptr(idx), P, Q, k, ptr(out_s), ptr(out_i), current_stream_ptr()),
+                  "evr_topk_merge")
+        else:
+            kp = 1 << (k - 1).bit_length()
+            scratch = torch.empty(Q * kp * 8, dtype=torch.uint8, device=scores.device)
+            check(lib.evr_topk_merge_large(ptr(scores), ptr(idx), P, Q, k, ptr(out_s), ptr(out_i), ptr(scratch),
+                                           scratch.numel(), current_stream_ptr()), "evr_topk_merge_large")
     return out_s, out_i
 
 

@@ -46,9 +46,10 @@ int evr_store_prepare(const void* src, int src_dtype, int64_t N, int D, void* ds
  * queries [Q, D] fp16
  * out_scores [Q, k] fp32 descending; out_idx [Q, k] int64 = row_offset + local row.
  * 1 <= k <= 1024.  If k > N the tail is filled with score -inf / idx -1.
- * For N >= 32768 the call first runs the same kernel over a sample of min(N/8, 65536) rows; the sample's k-th
- * best score per query is the admission threshold the full scan starts from (results are unchanged: it is a lower
- * bound on the global k-th best).
+ * For N >= 32768 the call first runs the same kernel over a sample of n0 rows (65536 at Q <= 128; at larger query
+ * batches max(65536, min(3072 k, N/16)); never more than N/4; tiles strided evenly across the whole store) recording
+ * only the maximum of every 64-row group; the k-th largest group maximum per query is the admission threshold the full
+ * scan starts from (results are unchanged: it is a lower bound on the global k-th best).
  * workspace: evr_topk_workspace_bytes(N, D, Q, k) bytes of device memory. */
 int evr_topk_workspace_bytes(int64_t N, int D, int Q, int k, size_t* out_bytes);
 int evr_topk_search(const void* store, int64_t N, int D, int64_t row_offset, const void* queries, int Q, int k,
@@ -58,6 +59,18 @@ int evr_topk_search(const void* store, int64_t N, int D, int64_t row_offset, con
  * scores [P, Q, k] fp32, idx [P, Q, k] int64  ->  out [Q, k]. */
 int evr_topk_merge(const float* scores, const int64_t* idx, int P, int Q, int k, float* out_scores,
                    int64_t* out_idx, void* stream);
+
+/* Any top_k (the reference sorts all N scores, embedding_service.py:317-320, so it has no upper limit): requests
+ * with k > 1024 run as a score pass (each store row read once per chunk of 8 queries, [8, N] fp32 written to the
+ * workspace) followed by a per-query radix select + sort over global memory.  1 <= k <= N; same outputs and tie rule
+ * (score desc, row asc) as evr_topk_search.  evr_topk_merge_large is the cross-shard merge for such k
+ * (scratch >= Q * pow2ceil(k) * 8 bytes). */
+int evr_topk_large_workspace_bytes(int64_t N, int Q, int64_t k, size_t* out_bytes);
+int evr_topk_search_large(const void* store, int64_t N, int D, int64_t row_offset, const void* queries, int Q,
+                          int64_t k, float* out_scores, int64_t* out_idx, void* workspace, size_t workspace_bytes,
+                          void* stream);
+int evr_topk_merge_large(const float* scores, const int64_t* idx, int P, int Q, int64_t k, float* out_scores,
+                         int64_t* out_idx, void* scratch, size_t scratch_bytes, void* stream);
 
 /* per-candidate re-score: replaces np.dot(embeddings[i:i+1], q.T)[0][0]
  * (embedding_service.py:274-279).  rows [R] int64 local row ids; out [R] fp32. */

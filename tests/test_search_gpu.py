@@ -227,3 +227,123 @@ def test_full_size_properties(pkg, cuda, N):
     for j in range(Q):
         assert so.topk_equal_up_to_ties(idx[j].cpu().numpy(), sc[j].cpu().numpy(), best_i[j].cpu().numpy(),
                                         best_s[j].cpu().numpy(), 1e-5)
+
+
+# ---- any top_k (the reference sorts all N scores: embedding_service.py:317-320) ------------------------------------
+@pytest.mark.parametrize("N,Q,k", [(5_000, 3, 2_000), (5_000, 11, 1_025), (1_500, 2, 1_500), (40_000, 9, 4_097)])
+def test_large_k_matches_oracle(pkg, cuda, N, Q, k):
+    """k > 1024 leaves the fused kernel (score pass + radix select over global memory); same contract."""
+    rng = np.random.default_rng(N + k)
+    raw = rng.standard_normal((N, 512)).astype(np.float32)
+    raw[N // 2] = raw[N // 3]  # an exact tie somewhere in the middle: broken by ascending row
+    q = _unit(rng.standard_normal((Q, 512)).astype(np.float32))
+    sc, idx = _check(pkg, cuda, raw, q, k, row_offset=7_000)
+    assert sc.shape == (Q, k)
+
+
+def test_large_k_through_the_service_contract(pkg, cuda):
+    """top_k * 3 > 1024 used to raise inside FrameStore.search and come back as [] from the service."""
+    rng = np.random.default_rng(41)
+    raw = rng.standard_normal((3_000, 512)).astype(np.float32)
+    q = _unit(rng.standard_normal((1, 512)).astype(np.float32))
+    store = pkg.search.FrameStore.from_numpy(raw, device=cuda)
+    sc, idx = store.search(torch.from_numpy(q).to(cuda), 400 * 3)
+    ref_i, ref_s = so.batched_topk(so.normalise_store(raw), q, 1200)
+    assert so.topk_equal_up_to_ties(idx[0].cpu().numpy(), sc[0].cpu().numpy(), ref_i[0], ref_s[0], EPS)
+
+
+def test_large_k_merge_matches_numpy(pkg, cuda):
+    rng = np.random.default_rng(43)
+    P, Q, k = 3, 5, 1_500
+    sc = rng.standard_normal((P, Q, k)).astype(np.float32)
+    sc[1, :, 1_400:] = -np.inf
+    idx = rng.permutation(P * Q * k).reshape(P, Q, k).astype(np.int64)
+    idx[1, :, 1_400:] = -1
+    ms, mi = pkg.search.merge_topk(torch.from_numpy(sc).to(cuda), torch.from_numpy(idx).to(cuda))
+    ms, mi = ms.cpu().numpy(), mi.cpu().numpy()
+    for j in range(Q):
+        flat_s, flat_i = sc[:, j].ravel(), idx[:, j].ravel()
+        order = np.lexsort((flat_i, -flat_s))[:k]
+        assert np.array_equal(ms[j], flat_s[order]) and np.array_equal(mi[j], flat_i[order])
+
+
+# ---- stores that are not iid: the sample pass must stay a valid (and useful) lower bound --------------------------
+def _torch_reference_topk(rows_fp16, q_fp16, k, chunk=500_000):
+    """Chunked fp32 scan of the same fp16 operands (checker for stores too large for the numpy oracle)."""
+    Q, N = q_fp16.shape[0], rows_fp16.shape[0]
+    dev = rows_fp16.device
+    best_s = torch.full((Q, k), -float("inf"), device=dev)
+    best_i = torch.full((Q, k), -1, dtype=torch.int64, device=dev)
+    for r0 in range(0, N, chunk):
+        s = q_fp16.float() @ rows_fp16[r0:r0 + chunk].float().t()
+        cs, ci = torch.cat([best_s, s], 1).topk(k, dim=1)
+        all_i = torch.cat([best_i, torch.arange(r0, r0 + s.shape[1], device=dev).expand(Q, -1)], 1)
+        best_s, best_i = cs, all_i.gather(1, ci)
+    return best_s, best_i
+
+
+@pytest.mark.parametrize("layout", ["clustered", "ascending", "descending", "mass_ties"])
+@pytest.mark.parametrize("Q", [4, 300])
+def test_structured_stores(pkg, cuda, layout, Q):
+    """Real stores are laid out video by video in temporal order (near-duplicate neighbours, drifting content), not
+    iid: clustered rows, rows sorted by their score against the query direction (both ways: the threshold either
+    never settles or the best rows come last), and mass exact ties (which overflow the select kernel's shared-memory
+    staging and take its global-memory passes).  Checked against a chunked fp32 scan of the same fp16 operands."""
+    g = torch.Generator(device=cuda).manual_seed(hash(layout) % 1000 + Q)
+    N, k = 200_000, 100
+    base = torch.randn((Q, 512), generator=g, device=cuda)
+    base = base / base.norm(dim=-1, keepdim=True)
+    if layout == "clustered":       # 200 "videos" of 1000 near-duplicate frames each
+        centres = torch.randn((200, 512), generator=g, device=cuda)
+        rows = centres.repeat_interleave(1000, 0) + 0.05 * torch.randn((N, 512), generator=g, device=cuda)
+    elif layout in ("ascending", "descending"):
+        rows = torch.randn((N, 512), generator=g, device=cuda)
+        score = (rows / rows.norm(dim=-1, keepdim=True)) @ base[0]
+        rows = rows[torch.argsort(score, descending=(layout == "descending"))]
+    else:                           # 60 % of the store is one of 3 vectors: thousands of exact ties per query
+        rows = torch.randn((N, 512), generator=g, device=cuda)
+        pick = torch.randint(0, 5, (N,), generator=g, device=cuda)
+        for j in range(3):
+            rows[pick == j] = base[j % Q] * 2.0
+    store = pkg.search.FrameStore.from_tensor(rows, device=cuda)
+    q = base.half()
+    sc, idx = store.search(q, k)
+    ref_s, ref_i = _torch_reference_topk(store.rows, q, k)
+    assert torch.allclose(sc, ref_s, atol=1e-5)
+    for j in range(Q):
+        assert so.topk_equal_up_to_ties(idx[j].cpu().numpy(), sc[j].cpu().numpy(), ref_i[j].cpu().numpy(),
+                                        ref_s[j].cpu().numpy(), 1e-5), (layout, j)
+        assert len(set(idx[j].tolist())) == k
+    if layout == "mass_ties":       # ties broken by ascending row id, exactly
+        tied = (rows.half().float() @ q[0].float() > 1.9).nonzero().flatten()[:k]
+        assert torch.equal(idx[0], tied)
+
+
+def test_full_size_cta_pair_path(pkg, cuda):
+    """The configuration bench.py times (BASELINE config 3): 10 M x 512 fp16 rows, a query batch large enough for the
+    CTA-pair kernel (topk_scan_kernel<16, 2>), the 307 200-row strided sample pass and the multi-slice plan.  64 random
+    queries of the batch are compared with a chunked fp32 scan of the same operands; every list is checked for order,
+    range and duplicates; planted rows must come first."""
+    N, Q, k = 10_000_000, 1_024, 100
+    g = torch.Generator(device=cuda).manual_seed(2)
+    rows = torch.empty((N, 512), dtype=torch.float16, device=cuda)
+    for r0 in range(0, N, 1_000_000):
+        x = torch.randn((1_000_000, 512), generator=g, device=cuda)
+        rows[r0:r0 + 1_000_000] = (x / x.norm(dim=-1, keepdim=True)).half()
+        del x
+    q = torch.randn((Q, 512), generator=g, device=cuda)
+    q = (q / q.norm(dim=-1, keepdim=True)).half()
+    planted = torch.randperm(N, generator=g, device=cuda)[:Q]
+    rows[planted] = q
+    store = pkg.search.FrameStore(rows)
+    sc, idx = store.search(q, k)
+    assert torch.equal(idx[:, 0], planted)
+    assert torch.all(sc[:, 1:] <= sc[:, :-1]) and int(idx.min()) >= 0 and int(idx.max()) < N
+    srt = idx.sort(dim=1).values
+    assert bool((srt[:, 1:] != srt[:, :-1]).all()), "duplicate row in a result list"
+    pick = torch.randperm(Q, generator=g, device=cuda)[:64]
+    ref_s, ref_i = _torch_reference_topk(rows, q[pick], k, chunk=1_000_000)
+    assert torch.allclose(sc[pick], ref_s, atol=1e-5)
+    for j, p in enumerate(pick.tolist()):
+        assert so.topk_equal_up_to_ties(idx[p].cpu().numpy(), sc[p].cpu().numpy(), ref_i[j].cpu().numpy(),
+                                        ref_s[j].cpu().numpy(), 1e-5), p
