@@ -25,7 +25,7 @@ from pathlib import Path
 
 from . import clip as _clip
 from .preprocess import GpuPreprocess
-from .search import FrameStore
+from .search import FrameStore, shard_bounds
 
 IMAGE_EXT = ('.jpg', '.jpeg', '.png')  # embedding_service.py:452
 
@@ -248,6 +248,49 @@ class DataService:
 
 def _pyfloat(x):
     return float(x) if type(x).__module__ == "numpy" else x
+
+
+def _dist_context(rank=None, world=None, barrier=None):
+    """(rank, world, barrier) of a data-parallel call: explicit arguments win, else the initialised process group,
+    else one process.  `barrier` is a callable every rank calls at the same points."""
+    if rank is None or world is None:
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized():
+            rank, world = dist.get_rank(), dist.get_world_size()
+            barrier = barrier or dist.barrier
+        else:
+            rank, world = 0, 1
+    if world > 1 and barrier is None:
+        import torch.distributed as dist
+        if not (dist.is_available() and dist.is_initialized()):
+            raise ValueError("world > 1 needs an initialised torch.distributed process group or an explicit barrier=")
+        barrier = dist.barrier
+    return int(rank), int(world), (barrier or (lambda: None))
+
+
+def shard_rows_to_npy(path, n_rows, lo, rows, rank=0, world=1, barrier=None):
+    """One `<video>_embeddings.npy` ([n_rows, D], the layout of embedding_service.py:505) written by `world` ranks,
+    rank r holding rows [lo, lo + len(rows)).  One rank: `np.save`.  Several: rank 0 creates the file at its final
+    size (`np.lib.format.open_memmap`: the same NPY v1 header `np.save` writes), a barrier, every rank writes its
+    slice through a memory map, a barrier.  No row crosses a link: the exchange is the shared file system."""
+    if world == 1:
+        np.save(path, rows)
+        return
+    barrier = barrier or (lambda: None)
+    mm = None
+    if rank == 0:
+        mm = np.lib.format.open_memmap(path, mode="w+", dtype=rows.dtype, shape=(int(n_rows), rows.shape[1]))
+    barrier()
+    if mm is None:
+        mm = np.load(path, mmap_mode="r+")
+        if mm.shape != (int(n_rows), rows.shape[1]) or mm.dtype != rows.dtype:
+            raise RuntimeError(f"{path}: rank {rank} sees {mm.shape} {mm.dtype}, expected {(n_rows, rows.shape[1])} "
+                               f"{rows.dtype}")
+    if len(rows):
+        mm[lo:lo + len(rows)] = rows
+    mm.flush()
+    del mm
+    barrier()
 
 
 def decode_frames(paths, workers=None, window=None):
@@ -533,13 +576,20 @@ class EmbeddingService:
             print(f"Error extracting embedding from {image_path}: {e}")
             return None
 
-    def extract_and_save_embeddings_from_folder(self, folder_path, model_name=None, video_name=None):
+    def extract_and_save_embeddings_from_folder(self, folder_path, model_name=None, video_name=None, rank=None,
+                                                world=None, barrier=None):
         """Encode every frame of a folder (sorted file names) and write `<video>_embeddings.npy` [N, D] unit-norm
         (:425-536).  Returns the path, or None when the folder has no images.  Differences from the reference, all
         from SURVEY.md 8g: the model is chosen per call without flipping `active_model` under other threads; an
         unknown video gets `<embedding_dir>/<video>_embeddings.npy` instead of overwriting the first video's file;
-        an undecodable frame becomes a zero row (not a NameError / NaN row)."""
-        from PIL import Image
+        an undecodable frame becomes a zero row (not a NameError / NaN row).
+
+        Data-parallel ingest (SURVEY.md 8e "Encode"; absent from the reference, which is single-device): when
+        `torch.distributed` is initialised (or `rank` / `world` are given) every rank calls this with the same
+        arguments, the sorted frame list is cut into contiguous rank slices (`search.shard_bounds`), each rank encodes
+        its slice and writes its rows into one pre-sized `.npy` (`shard_rows_to_npy`), and rank 0 stamps the metadata.
+        Frames are independent, so there is no collective on the data path; row i of the file is bit for bit the row
+        a single GPU writes (the tower is batch-invariant, the final normalisation is per row)."""
         key = self.active_model
         if model_name:
             key = "original" if (model_name == "finetuned" and self.finetuned_model is None) else model_name
@@ -556,8 +606,29 @@ class EmbeddingService:
         if not frame_files:
             print(f"No image files found in {folder_path}")
             return None
+        rank, world, barrier = _dist_context(rank, world, barrier)
+        lo, hi = shard_bounds(len(frame_files), world, rank)
+        embeddings, bad_rows = self._encode_frames(folder_path, frame_files[lo:hi], key)
+        norm = np.linalg.norm(embeddings, axis=-1, keepdims=True)
+        embeddings = embeddings / np.where(norm > 1e-8, norm, 1).astype(embeddings.dtype)
+        embeddings[bad_rows] = 0
+        shard_rows_to_npy(embeddings_path, len(frame_files), lo, embeddings, rank, world, barrier)
+        if rank == 0:
+            self._stamp_metadata(video_name, key)
+        return embeddings_path
+
+    def _embedding_dtype(self, key):
+        if key == "finetuned" and self.finetuned_model is not None:
+            return np.float32
+        return np.float16 if getattr(self.original_model, "dtype", torch.float32) == torch.float16 else np.float32
+
+    def _encode_frames(self, folder_path, frame_files, key):
+        """-> ([n, D] un-normalised rows of these files in the model dtype, indices of undecodable frames)."""
+        from PIL import Image
         S = self.original_model.visual.input_resolution
         all_embeddings, bad_rows = [], []
+        if not frame_files:   # more ranks than frames
+            return np.zeros((0, self.original_model.visual.output_dim), self._embedding_dtype(key)), bad_rows
         if getattr(self.preprocess, "evr_n_px", None) == S and self.gpu_preprocess:
             # device path: PIL only decodes; Resize(bicubic) + CenterCrop run on the GPU bit-identically to PIL
             # (preprocess.py) and ToTensor + Normalize are fused into the encoder's im2col.  Frames of one size are
@@ -605,13 +676,7 @@ class EmbeddingService:
                         batch.append(torch.zeros(3, S, S))
                         bad_rows.append(i + j)
                 all_embeddings.append(self._encode_images(torch.stack(batch).to(self.device), key))
-        embeddings = np.vstack(all_embeddings)
-        norm = np.linalg.norm(embeddings, axis=-1, keepdims=True)
-        embeddings = embeddings / np.where(norm > 1e-8, norm, 1).astype(embeddings.dtype)
-        embeddings[bad_rows] = 0
-        np.save(embeddings_path, embeddings)
-        self._stamp_metadata(video_name, key)
-        return embeddings_path
+        return np.vstack(all_embeddings), bad_rows
 
     def _stamp_metadata(self, video_name, model_key):
         """:509-526 -- record which model produced the store in the video's metadata JSON."""
