@@ -9,9 +9,11 @@ The reference does `import clip` (un-vendored submodule Backend/CLIP = openai/CL
 libevr.so).  Put this module on sys.path as `clip` and the reference's service code runs unchanged.
 
 Weights: openai checkpoints are fetched from the network by the original `clip.load`; this box has none, so `load`
-takes them from (1) an explicit `state_dict=`, (2) `<download_root>/<name with / -> ->.pt` (a torch-saved
-openai-keyed state_dict or a checkpoint dict with "state_dict"/"model_state_dict"), else (3) raises -- unless
-`random_init=<seed>` (or EVR_CLIP_RANDOM_INIT=<seed>) asks for seeded openai-scale random weights (benchmarks).
+takes them from (1) an explicit `state_dict=`, (2) `<download_root>/<name with / -> ->.pt` -- OpenAI's own file (a
+TorchScript archive, opened with `torch.jit.load` as the original does), a torch-saved openai-keyed state_dict, or a
+checkpoint dict with "state_dict"/"model_state_dict" -- else (3) raises, unless `random_init=<seed>` (or
+EVR_CLIP_RANDOM_INIT=<seed>) asks for seeded openai-scale random weights (benchmarks; announced loudly on stderr).
+`clip.load(<path to a checkpoint file>)` reads the geometry off the tensors (`infer_model_name`).
 """
 import os
 
@@ -101,6 +103,43 @@ def _find_checkpoint(name, download_root):
     root = download_root or os.environ.get("EVR_CLIP_ROOT") or os.path.expanduser("~/.cache/clip")
     path = os.path.join(root, name.replace("/", "-") + ".pt")
     return path if os.path.isfile(path) else None
+
+
+def _load_checkpoint_file(path):
+    """A weights file -> whatever it holds (module or dict), the way openai's `clip.load` opens one: OpenAI's
+    `ViT-B-32.pt` / `ViT-L-14.pt` are TorchScript archives (`torch.jit.load(...).state_dict()`), fine-tuned checkpoints
+    (`torch.save({'model_state_dict': ...})`, embedding_service.py:112-113) are pickled dicts.  Pickles are opened with
+    `weights_only=True`; a checkpoint that needs arbitrary unpickling is refused unless EVR_CLIP_TRUSTED_CHECKPOINTS=1."""
+    import zipfile
+    is_script = False
+    if zipfile.is_zipfile(path):
+        with zipfile.ZipFile(path) as z:
+            is_script = any(n.endswith("constants.pkl") for n in z.namelist())
+    if is_script:
+        return torch.jit.load(path, map_location="cpu").eval().state_dict()
+    try:
+        return torch.load(path, map_location="cpu", weights_only=True)
+    except Exception as e:
+        if os.environ.get("EVR_CLIP_TRUSTED_CHECKPOINTS") == "1":
+            return torch.load(path, map_location="cpu", weights_only=False)
+        raise RuntimeError(f"{path}: not loadable as a TorchScript archive or a plain tensor checkpoint ({e}); set "
+                           "EVR_CLIP_TRUSTED_CHECKPOINTS=1 to unpickle a trusted file") from e
+
+
+def infer_model_name(state_dict):
+    """The geometry a state_dict belongs to, read off its tensors the way openai's `build_model` does (vision width
+    = conv1 rows, patch = conv1 kernel, layers = resblocks with an in_proj_weight): -> a key of GEOMETRY."""
+    conv = state_dict.get("visual.conv1.weight")
+    if conv is None:
+        raise RuntimeError("checkpoint holds no vision tower (visual.conv1.weight)")
+    width, patch = int(conv.shape[0]), int(conv.shape[-1])
+    layers = len({k.split(".")[3] for k in state_dict
+                  if k.startswith("visual.transformer.resblocks.") and k.endswith(".attn.in_proj_weight")})
+    for name, g in GEOMETRY.items():
+        if (g["width"], g["patch"], g["layers"]) == (width, patch, layers):
+            return name
+    raise RuntimeError(f"unsupported vision tower: width {width}, patch {patch}, {layers} layers; available models = "
+                       f"{available_models()}")
 
 
 def _unwrap(obj):
@@ -223,13 +262,14 @@ def load(name, device="cuda", jit=False, download_root=None, state_dict=None, ra
     """clip.load(name, device, jit=False) -> (model, preprocess).  See the module docstring for weight lookup."""
     if name not in _MODELS:
         if os.path.isfile(name):
-            state_dict, name = _unwrap(torch.load(name, map_location="cpu", weights_only=False)), "ViT-B/32"
+            state_dict = _unwrap(_load_checkpoint_file(name))
+            name = infer_model_name(state_dict)
         else:
             raise RuntimeError(f"Model {name} not found; available models = {available_models()}")
     if state_dict is None:
         path = _find_checkpoint(name, download_root)
         if path is not None:
-            state_dict = _unwrap(torch.load(path, map_location="cpu", weights_only=False))
+            state_dict = _unwrap(_load_checkpoint_file(path))
     if state_dict is None:
         seed = random_init if random_init is not None else os.environ.get("EVR_CLIP_RANDOM_INIT")
         if seed is None:
@@ -237,6 +277,9 @@ def load(name, device="cuda", jit=False, download_root=None, state_dict=None, ra
                 f"no weights for {name}: this box has no network, put an openai-keyed state_dict at "
                 f"{os.path.join(download_root or '~/.cache/clip', name.replace('/', '-') + '.pt')} "
                 "(or pass state_dict=..., or random_init=<seed> for benchmarking)")
+        import sys
+        print(f"WARNING: clip.load({name!r}): no checkpoint found -- serving seeded RANDOM weights (seed {int(seed)}); "
+              "embeddings are meaningless outside benchmarks and parity tests", file=sys.stderr)
         state_dict = random_visual_state_dict(name, int(seed))
         state_dict.update(random_text_state_dict(name, int(seed)))
     else:

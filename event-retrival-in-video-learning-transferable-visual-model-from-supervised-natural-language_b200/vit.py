@@ -120,6 +120,10 @@ class VisionEncoder:
                         or stage[slot].shape[1:] != hb.shape[1:]:
                     stage[slot] = torch.empty((max(B, 1),) + tuple(hb.shape[1:]), dtype=hb.dtype, device=dev)
                     ev_free[slot] = None
+                    # the caching allocator may hand back a block that compute-stream work still in flight is
+                    # reading (a previous encode's temporary, an embedding whose D2H copy is pending): the copy
+                    # stream must not write it before that work has drained
+                    copy.wait_stream(comp)
                 if out_host[slot] is None or out_host[slot].shape[0] < B or out_host[slot].dtype != out_dtype:
                     out_host[slot] = torch.empty((max(B, 1), self.out_dim), dtype=out_dtype).pin_memory()
                 with torch.cuda.stream(copy):

@@ -64,7 +64,7 @@ def test_nccl_sharded_search_matches_oracle(tmp_path, N, Q, k):
     s, i = outs[0]["s"], outs[0]["i"]
     assert s.shape == (Q, k)
     for j in range(Q):
-        assert so.topk_equal_up_to_ties(i[j, :kk], s[j, :kk], ref_i[j], ref_s[j], 2.0 ** -9)
+        assert so.topk_equal_up_to_ties(i[j, :kk], s[j, :kk], ref_i[j], ref_s[j], 2.0 ** -10)
         assert (i[j, kk:] == -1).all() and np.isneginf(s[j, kk:]).all()   # fewer rows than k: padded tail
 
 
@@ -86,7 +86,7 @@ def test_one_process_two_devices(pkg):
         store = pkg.search.FrameStore.from_numpy(raw, device=dev)
         sc, idx = store.search(torch.from_numpy(q).to(dev), 200)     # k > 128: the large select configuration
         for j in (0, 77, 149):
-            assert so.topk_equal_up_to_ties(idx[j].cpu().numpy(), sc[j].cpu().numpy(), ref_i[j], ref_s[j], 2.0 ** -9)
+            assert so.topk_equal_up_to_ties(idx[j].cpu().numpy(), sc[j].cpu().numpy(), ref_i[j], ref_s[j], 2.0 ** -10)
         enc = pkg.vit.VisionEncoder.from_state_dict(sd, "ViT-B/32", device=dev, max_batch=8, prefix="visual.")
         embs.append(enc.encode(frames.to(dev), normalise=True).cpu())
     assert torch.equal(embs[0], embs[1])

@@ -48,7 +48,7 @@ def test_search_across_videos_matches_oracle(pkg, cuda, tmp_path):
     sc, idx = store.search(torch.from_numpy(q), 50)
     ref_i, ref_s = so.batched_topk(emb, q, 50)
     for j in range(5):
-        assert so.topk_equal_up_to_ties(idx[j].cpu().numpy(), sc[j].cpu().numpy(), ref_i[j], ref_s[j], 2.0 ** -9)
+        assert so.topk_equal_up_to_ties(idx[j].cpu().numpy(), sc[j].cpu().numpy(), ref_i[j], ref_s[j], 2.0 ** -10)
     hits = store.search_frames(q[0], 10)
     assert [(v, f) for v, f, _ in hits] == [names[i] for i in idx[0, :10].cpu().numpy()]
     assert all(isinstance(s, float) for _, _, s in hits) and hits[0][2] >= hits[-1][2]

@@ -114,7 +114,7 @@ def test_clip_model_text_and_service_query_path(pkg, cuda, tower, tmp_path, monk
     ref_i, ref_s = so.batched_topk(so.normalise_store(raw), q.astype(np.float32), 10)
     pairs = svc.search_with_scores(q, 10)
     got_i = np.array([int(f.split(".")[0]) for f in got])
-    assert so.topk_equal_up_to_ties(got_i, np.array([s for _, s in pairs]), ref_i[0], ref_s[0], 2.0 ** -9)
+    assert so.topk_equal_up_to_ties(got_i, np.array([s for _, s in pairs]), ref_i[0], ref_s[0], 2.0 ** -10)
     assert abs(svc.extract_query_confidence(got[0], query) - pairs[0][1]) < 1e-5
 
 
