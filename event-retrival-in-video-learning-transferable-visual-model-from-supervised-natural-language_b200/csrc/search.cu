@@ -21,6 +21,8 @@
 //            never exists in memory.
 #include <cuda_fp16.h>
 
+#include <cstdlib>
+
 #include "../../include/evr.h"
 #include "common.cuh"
 #include "ptx.cuh"
@@ -1005,7 +1007,10 @@ extern "C" int evr_topk_search(const void* store, int64_t N, int D, int64_t row_
   const float* init = nullptr;
   if (p.n0 > 0) {
     const int rowtile = kScanRowTile * p.pre.cg;
-    const int64_t stride = (N / rowtile) / (p.n0 / rowtile);  // >= 4: n0 <= N / 4, whole tiles only
+    int64_t stride = (N / rowtile) / (p.n0 / rowtile);  // >= 4: n0 <= N / 4, whole tiles only
+    if (const char* e = getenv("EVR_SAMPLE_PREFIX")) {  // A/B knob: sample the first n0 rows instead
+      if (e[0] == '1') stride = 1;
+    }
     if (int r = run_scan(p.pre, store, p.n0, N, static_cast<int>(stride), D, queries, Q, k, nullptr, nullptr, nullptr,
                          gmax, p.groups, s)) return r;
     {

@@ -293,6 +293,21 @@ def shard_rows_to_npy(path, n_rows, lo, rows, rank=0, world=1, barrier=None):
     barrier()
 
 
+def encode_frames_sharded(encoder, host_batches, n_rows, lo, path, rank=None, world=None, barrier=None,
+                          out_dtype=torch.float16):
+    """The data-parallel ingest without its JPEG decode: this rank's contiguous slice of a frame list, already decoded
+    (`host_batches`: pinned uint8 [B,S,S,3] or float [B,3,S,S] host tensors, global rows [lo, lo + sum(B))), goes
+    through `VisionEncoder.encode_stream` (H2D copy of batch i+1 under the tower pass of batch i, embeddings back to
+    pinned memory) and the unit-norm rows land in the one `.npy` of `n_rows` rows every rank writes
+    (`shard_rows_to_npy`).  Returns this rank's rows.  What `extract_and_save_embeddings_from_folder` does after PIL."""
+    rank, world, barrier = _dist_context(rank, world, barrier)
+    rows = [e.numpy() for e in encoder.encode_stream(host_batches, normalise=True, out_dtype=out_dtype)]
+    rows = np.concatenate(rows) if rows else np.zeros((0, encoder.out_dim),
+                                                      np.float16 if out_dtype == torch.float16 else np.float32)
+    shard_rows_to_npy(path, n_rows, lo, rows, rank, world, barrier)
+    return rows
+
+
 def decode_frames(paths, workers=None, window=None):
     """Ordered, bounded-lookahead JPEG decode on host threads: yields `np.uint8 [H, W, 3]` (or the exception that the
     decode raised) for every path, in order.  The reference decodes one frame at a time on the request thread

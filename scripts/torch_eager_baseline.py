@@ -42,13 +42,36 @@ class EagerViT(nn.Module):
         self.register_buffer("mean", torch.tensor([0.48145466, 0.4578275, 0.40821073]).view(1, 3, 1, 1) * 255)
         self.register_buffer("std", torch.tensor([0.26862954, 0.26130258, 0.27577711]).view(1, 3, 1, 1) * 255)
 
+    @torch.no_grad()
+    def load_openai_state_dict(self, sd, prefix="visual."):
+        """Same weights as the product's tower: openai/CLIP VisionTransformer keys -> this module's names."""
+        def put(param, key):
+            param.copy_(sd[prefix + key].reshape(param.shape))
+        put(self.conv.weight, "conv1.weight")
+        put(self.cls, "class_embedding")
+        put(self.pos, "positional_embedding")
+        put(self.proj, "proj")
+        for ln, key in ((self.ln_pre, "ln_pre"), (self.ln_post, "ln_post")):
+            put(ln.weight, key + ".weight")
+            put(ln.bias, key + ".bias")
+        for i, blk in enumerate(self.blocks):
+            b = f"transformer.resblocks.{i}."
+            for mod, key in ((blk.ln_1, "ln_1"), (blk.ln_2, "ln_2"), (blk.out, "attn.out_proj"), (blk.fc, "mlp.c_fc"),
+                             (blk.proj, "mlp.c_proj")):
+                put(mod.weight, b + key + ".weight")
+                put(mod.bias, b + key + ".bias")
+            put(blk.qkv.weight, b + "attn.in_proj_weight")
+            put(blk.qkv.bias, b + "attn.in_proj_bias")
+        return self
+
     def forward(self, frames_u8):  # [B, H, W, 3] uint8, as bench.py feeds our tower
         x = ((frames_u8.permute(0, 3, 1, 2).to(self.mean.dtype) - self.mean) / self.std)
         x = self.conv(x).flatten(2).transpose(1, 2)
         x = torch.cat([self.cls.expand(x.shape[0], 1, -1), x], 1) + self.pos
         x = self.blocks(self.ln_pre(x))
         e = self.ln_post(x[:, 0]) @ self.proj
-        return F.normalize(e.float(), dim=-1).half()
+        e = F.normalize(e.float(), dim=-1)
+        return e if self.proj.dtype == torch.float32 else e.half()
 
 
 def timed(fn, steps, warmup=3):
