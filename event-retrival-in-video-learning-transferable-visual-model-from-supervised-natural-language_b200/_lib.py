@@ -59,6 +59,7 @@ SIGNATURES = {
                                 ctypes.POINTER(c_void_p)]),
     "evr_text_destroy": (c_int, [c_void_p]),
     "evr_text_encode": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_void_p]),
+    "evr_attention": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "evr_gemm_bf16": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
 }
 for _name, (_res, _args) in SIGNATURES.items():

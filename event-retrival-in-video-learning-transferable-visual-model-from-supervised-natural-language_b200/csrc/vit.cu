@@ -228,3 +228,11 @@ extern "C" int evr_vit_encode(evr_vit* h, const void* pixels, int pix_dtype, int
   }
   return 0;
 }
+
+extern "C" int evr_attention(const void* qkv, void* out, int B, int L, int d, int heads, int causal, int impl,
+                             void* stream) {
+  EVR_REQUIRE(qkv && out, "evr_attention: null pointer");
+  EVR_REQUIRE(B >= 1 && L >= 1 && impl >= 0 && impl <= 2, "evr_attention: bad arguments B=%d L=%d impl=%d", B, L, impl);
+  return launch_attention_impl(static_cast<const __nv_bfloat16*>(qkv), static_cast<__nv_bfloat16*>(out), B, L, d, heads,
+                               causal, impl, static_cast<cudaStream_t>(stream));
+}

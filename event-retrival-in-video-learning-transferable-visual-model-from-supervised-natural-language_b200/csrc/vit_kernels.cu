@@ -1,6 +1,7 @@
 // Non-GEMM kernels of the CLIP vision tower: im2col(+normalise), cls rows, LayerNorm, attention core,
 // final L2-normalise/cast and the one-off weight repacking.  Structure follows openai/CLIP
 // clip/model.py VisionTransformer.forward / ResidualAttentionBlock.
+#include <cstdlib>
 #include <climits>
 
 #include "vit_kernels.cuh"
@@ -623,9 +624,25 @@ attention_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restric
   }
 }
 
+static bool attention_tc_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("EVR_ATTN_MMA_SYNC");  // A/B knob: keep the warp-level MMA core for every length
+    on = (e && e[0] == '1') ? 0 : 1;
+  }
+  return on == 1;
+}
+
 int launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int d, int heads, int causal,
                      cudaStream_t stream) {
+  return launch_attention_impl(qkv, out, B, L, d, heads, causal, 0, stream);
+}
+
+int launch_attention_impl(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int d, int heads, int causal,
+                          int impl, cudaStream_t stream) {
   EVR_REQUIRE(heads * 64 == d, "attention: head dim must be 64 (d=%d heads=%d)", d, heads);
+  if (impl == 2 || (impl == 0 && attention_tc_enabled() && attention_tc_supported(L, d, heads)))
+    return launch_attention_tc(qkv, out, B, L, d, heads, causal, stream);
   if (L <= 64 && !causal) {
     static PerDeviceMax configured_short;
     if (configured_short.needs(2 * kAttnStageBytes)) {

@@ -23,6 +23,13 @@ int launch_layernorm(const float* in, size_t in_stride, void* out, size_t out_st
 // softmax(q k^T / sqrt(hd) [+ causal mask]) v per (sequence, head); qkv bf16 [B*L, 3d] (q | k | v), out bf16 [B*L, d]. hd = 64.
 int launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int d, int heads, int causal,
                      cudaStream_t stream);
+// the same on tcgen05 / TMEM (attention_tc.cu), 64 < L <= 257; launch_attention dispatches to it
+bool attention_tc_supported(int L, int d, int heads);
+int launch_attention_tc(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int d, int heads, int causal,
+                        cudaStream_t stream);
+// impl 0: dispatch (tcgen05 where supported), 1: warp-level MMA kernels, 2: tcgen05 or an error
+int launch_attention_impl(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int d, int heads, int causal,
+                          int impl, cudaStream_t stream);
 
 // text tower: x = token_embedding[tokens] + positional_embedding ; EOT-row gather (argmax of the token ids)
 int launch_embed_tokens(const int32_t* tokens, const float* table, const float* pos, float* x, int B, int L, int d,

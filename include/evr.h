@@ -165,6 +165,13 @@ int evr_text_encode(evr_text* h, const int32_t* tokens, int B, void* out, int ou
 int evr_gemm_bf16(const void* A, const void* W, const float* bias, void* out, int M, int N, int K, int epilogue,
                   void* stream);
 
+/* building-block attention core exported for the parity tests: softmax(q k^T / 8 [+ causal mask]) v per
+ * (sequence, head), head dim 64.  qkv bf16 [B L, 3 d] (q | k | v as the in_proj GEMM writes it), out bf16 [B L, d].
+ * impl 0: what the towers use (tcgen05 / TMEM for 64 < L <= 257, warp-level MMA otherwise), 1: warp-level MMA kernels,
+ * 2: tcgen05 / TMEM kernel.  Replaces the core of nn.MultiheadAttention in clip/model.py ResidualAttentionBlock. */
+int evr_attention(const void* qkv_bf16, void* out_bf16, int B, int L, int d, int heads, int causal, int impl,
+                  void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,85 @@
+"""Attention core (building block behind `evr_attention`) against a plain PyTorch fp32 reference of the same op.
+
+softmax(q k^T / sqrt(64) [+ causal mask]) v per (sequence, head) on bf16 operands laid out as the in_proj GEMM writes
+them ([B L, 3 d], q | k | v).  Three implementations share the contract: the tcgen05 / TMEM kernel (impl 2: S and P V on
+the 5th-generation tensor cores, P kept in tensor memory), the warp-level MMA kernels (impl 1), and the dispatch the
+towers use (impl 0).  Tolerance: outputs are bf16 and P is rounded to bf16 before P V, so |err| <= 2^-7 relative to the
+largest |v| of the head (measured ~3e-3) and cosine >= 0.9999 per output row against the fp32 reference computed from
+the same bf16 inputs.
+"""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _reference(qkv, B, L, d, heads, causal):
+    x = qkv.float().view(B, L, 3, heads, 64).permute(2, 0, 3, 1, 4)      # [3, B, h, L, 64]
+    q, k, v = x[0], x[1], x[2]
+    s = q @ k.transpose(-1, -2) * 0.125
+    if causal:
+        s = s + torch.full((L, L), float("-inf"), device=s.device).triu_(1)
+    o = torch.softmax(s, dim=-1) @ v
+    return o.permute(0, 2, 1, 3).reshape(B * L, d)
+
+
+def _run(pkg, qkv, B, L, d, heads, causal, impl):
+    lib, check, ptr, stream = pkg._lib.lib, pkg._lib.check, pkg._lib.ptr, pkg._lib.current_stream_ptr
+    out = torch.full((B * L, d), float("nan"), dtype=torch.bfloat16, device=qkv.device)
+    check(lib.evr_attention(ptr(qkv), ptr(out), B, L, d, heads, int(causal), impl, stream()), "evr_attention")
+    torch.cuda.synchronize()
+    return out
+
+
+CASES = [  # B, L, d, heads, causal
+    (3, 257, 1024, 16, False),     # ViT-L/14: two full query tiles + the lone 257th token (as key and as query)
+    (5, 197, 768, 12, False),      # ViT-B/16: second tile partly filled, rows of the next image behind it
+    (4, 77, 512, 8, True),         # text tower, causal
+    (2, 77, 768, 12, True),        # ViT-L/14's text tower
+    (2, 65, 768, 12, False), (2, 128, 768, 12, False), (1, 256, 768, 12, False), (2, 129, 768, 12, True),
+    (40, 257, 1024, 16, False),    # 640 items: several per CTA, stage and region barriers wrap many times
+]
+
+
+@pytest.mark.parametrize("B,L,d,heads,causal", CASES)
+@pytest.mark.parametrize("impl", [2, 1, 0])
+def test_attention_matches_fp32_reference(pkg, cuda, B, L, d, heads, causal, impl):
+    g = torch.Generator(device=cuda).manual_seed(L * 7 + B)
+    qkv = torch.randn((B * L, 3 * d), generator=g, device=cuda)
+    qkv[:, :d] *= 2.0                      # sharper softmax than unit-variance scores give
+    qkv[::7, 2 * d:] += 3.0                # some rows of v stand out: a mis-weighted key shows
+    qkv = qkv.to(torch.bfloat16).contiguous()
+    ref = _reference(qkv, B, L, d, heads, causal)
+    out = _run(pkg, qkv, B, L, d, heads, causal, impl).float()
+    assert torch.isfinite(out).all()
+    err = (out - ref).abs().max().item()
+    scale = qkv[:, 2 * d:].float().abs().max().item()
+    cos = torch.nn.functional.cosine_similarity(out, ref, dim=-1).min().item()
+    assert err <= scale * 2.0 ** -7, (err, scale)
+    assert cos >= 0.9999, cos
+
+
+def test_tcgen05_kernel_is_what_the_towers_run(pkg, cuda):
+    """impl 0 dispatches 64 < L <= 257 to the tcgen05 kernel: bit-identical outputs; L = 50 stays on the short kernel."""
+    g = torch.Generator(device=cuda).manual_seed(3)
+    qkv = torch.randn((2 * 257, 3 * 1024), generator=g, device=cuda).to(torch.bfloat16)
+    assert torch.equal(_run(pkg, qkv, 2, 257, 1024, 16, False, 0), _run(pkg, qkv, 2, 257, 1024, 16, False, 2))
+    qkv = torch.randn((3 * 50, 3 * 768), generator=g, device=cuda).to(torch.bfloat16)
+    assert torch.equal(_run(pkg, qkv, 3, 50, 768, 12, False, 0), _run(pkg, qkv, 3, 50, 768, 12, False, 1))
+    with pytest.raises(pkg._lib.EvrError, match="unsupported shape"):
+        _run(pkg, qkv, 3, 50, 768, 12, False, 2)
+
+
+def test_rows_of_other_sequences_do_not_leak(pkg, cuda):
+    """The second query tile of a 197-token sequence is loaded as rows 128..255 -- the tail belongs to the next image (or
+    lies past the end of the buffer): changing those rows must not change this image's output."""
+    g = torch.Generator(device=cuda).manual_seed(9)
+    B, L, d, heads = 3, 197, 768, 12
+    qkv = torch.randn((B * L, 3 * d), generator=g, device=cuda).to(torch.bfloat16)
+    base = _run(pkg, qkv, B, L, d, heads, False, 2)
+    other = qkv.clone()
+    other[L:2 * L] = torch.randn((L, 3 * d), generator=g, device=cuda).to(torch.bfloat16) * 30
+    moved = _run(pkg, other, B, L, d, heads, False, 2)
+    assert torch.equal(moved[:L], base[:L]) and torch.equal(moved[2 * L:], base[2 * L:])
+    assert not torch.equal(moved[L:2 * L], base[L:2 * L])
