@@ -21,6 +21,7 @@
 //            never exists in memory.
 #include <cuda_fp16.h>
 
+#include <atomic>
 #include <cstdlib>
 
 #include "../../include/evr.h"
@@ -99,11 +100,16 @@ struct ScanArgs {
   int q_pad;           // num_qt * 128
   int cap;             // candidate-list capacity per (slice, query) = 32 * EPL
   const float* init_thresh;  // per-query admission threshold from the sample pass (nullptr: -inf)
-  int2* lists;         // [num_slices][q_pad][cap]  (score bits, local row): candidates of one (slice, query)
-  int* counts;         // [num_slices][q_pad]       entries used in each list
+  int ring;            // candidate lists per query: slice s appends to list s % ring (ring == num_slices: one each)
+  int2* lists;         // [ring][q_pad][cap]  (score bits, local row): candidates of one (list, query)
+  int* counts;         // [ring][q_pad]       entries used in each list
+  float* list_thresh;  // [ring][q_pad]       admission threshold a list's last item ended with
+  unsigned* done;      // [q_pad / 32][num_slices]  == epoch once the warp owning those 32 queries has finished the slice
+  unsigned epoch;      // unique per call (the workspace is reused)
   float* group_max;    // sample pass only (else nullptr): [q_pad][groups] max score of every 64-row group
   int groups;          // 64-row groups in the sample = N / 64
   int stages;          // depth of the store-row smem ring actually used (<= kScanStages; 2 at D = 768)
+  int row_evict_last;  // A/B knob (EVR_SCAN_EVICT_LAST=1): store rows stay in L2 as long as possible
   int tile_stride;     // sample pass: tile t of the launch reads store tile t * tile_stride (1 in the full scan)
 };
 
@@ -214,7 +220,8 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       // ===== TMA producer =====
       int stage = 0;
       uint32_t phase = 0, qphase = 0;
-      const uint64_t row_policy = args.num_qt > 1 ? kEvictNormal : kEvictFirst;
+      uint64_t row_policy = args.num_qt > 1 ? kEvictNormal : kEvictFirst;
+      if (args.row_evict_last) row_policy = kEvictLast;
       for (int item = unit; item < num_items; item += num_units) {
         const int qt = item % args.num_qt, slice = item / args.num_qt;
         mbar_wait(q_empty, qphase ^ 1);  // MMAs of the previous item no longer read the query tile
@@ -304,7 +311,8 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       const int q0 = (qt * CG + static_cast<int>(rank)) * kScanQTile + quad * 32;  // first query of this warp
       const bool q_valid = q0 + lane < args.Q;
       // the candidate list of (slice, query) is filled in place; the final select kernel reads it with its count
-      int2* const cand_warp = args.lists + (static_cast<size_t>(slice) * args.q_pad + q0) * cap;
+      const int ring_slot = slice % args.ring;
+      int2* const cand_warp = args.lists + (static_cast<size_t>(ring_slot) * args.q_pad + q0) * cap;
       int2* const buf = cand_warp + static_cast<size_t>(lane) * cap;
       // Admission is `score >= thresh`.  Any lower bound on the query's global k-th best score is a valid
       // threshold (at least k rows reach it): the sample pre-pass supplies one (init_thresh), and every local prune
@@ -312,6 +320,21 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       float thresh = q_valid ? (args.init_thresh ? __ldg(args.init_thresh + q0 + lane) : -INFINITY)
                              : __int_as_float(0x7fc00000);
       int cnt = 0;
+      if (args.group_max == nullptr && slice >= args.ring) {
+        // This list already holds the candidates of slice - ring (same queries, scanned by some other unit a few
+        // slices back): wait until that warp has published them, then go on from its count and its threshold.  Items
+        // run in slice-major order on resident CTAs, so the item waited for never depends on this one.
+        if (lane == 0) {
+          const volatile unsigned* f = args.done + static_cast<size_t>(q0 >> 5) * args.num_slices + (slice - args.ring);
+          while (*f != args.epoch) __nanosleep(200);
+        }
+        __syncwarp();
+        __threadfence();
+        if (q_valid) {
+          cnt = __ldcg(args.counts + static_cast<size_t>(ring_slot) * args.q_pad + q0 + lane);
+          thresh = fmaxf(thresh, __ldcg(args.list_thresh + static_cast<size_t>(ring_slot) * args.q_pad + q0 + lane));
+        }
+      }
       const int64_t t0 = static_cast<int64_t>(slice) * args.tiles_per_slice;
       int64_t t1 = t0 + args.tiles_per_slice;
       if (t1 > total_tiles) t1 = total_tiles;
@@ -382,7 +405,18 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         }
       }
       // ---- item done: the list stays where it is; publish its length
-      if (q_valid && args.counts != nullptr) args.counts[static_cast<size_t>(slice) * args.q_pad + q0 + lane] = cnt;
+      if (args.counts != nullptr) {
+        if (q_valid) {
+          __stcg(args.counts + static_cast<size_t>(ring_slot) * args.q_pad + q0 + lane, cnt);
+          __stcg(args.list_thresh + static_cast<size_t>(ring_slot) * args.q_pad + q0 + lane, thresh);
+        }
+        __threadfence();   // list entries, count and threshold before the flag
+        __syncwarp();
+        if (lane == 0) {
+          volatile unsigned* f = args.done + static_cast<size_t>(q0 >> 5) * args.num_slices + slice;
+          *f = args.epoch;
+        }
+      }
     }
   }
 
@@ -795,19 +829,19 @@ rescore_kernel(const __half* __restrict__ store, int64_t N, int D, const __half*
 // ============================================================================ host side
 struct ScanCore {  // one launch of topk_scan_kernel over N rows
   int cg;  // 1: one CTA per unit, 2: CTA pairs (cta_group::2)
-  int epl, cap, num_qt, q_pad, num_slices, tiles_per_slice, grid;
+  int epl, cap, num_qt, q_pad, num_slices, tiles_per_slice, grid, ring;
 };
 struct ScanPlan {
   ScanCore main, pre;
   int64_t n0;   // rows of the sample pass (0: none)
   int groups;   // n0 / 64
   int select_cap;  // candidate keys the select kernel can hold in shared memory
-  size_t lists_bytes, counts_bytes, gmax_bytes, thresh_bytes, total_bytes;
+  size_t lists_bytes, counts_bytes, gmax_bytes, thresh_bytes, lthresh_bytes, done_bytes, total_bytes;
 };
 
 static size_t up256(size_t x) { return (x + 255) & ~size_t(255); }
 
-static void plan_core(int64_t N, int Q, int k, int sm_total, ScanCore* p) {
+static void plan_core(int64_t N, int D, int Q, int k, int sm_total, ScanCore* p) {
   // more than one 128-query tile: CTA pairs (256 queries x 256-row tiles) halve the operand traffic per FLOP;
   // a single tile is HBM-bound and keeps one CTA per SM so every SM streams its own slice
   p->cg = (Q > kScanQTile && sm_total % 2 == 0) ? 2 : 1;
@@ -842,9 +876,35 @@ static void plan_core(int64_t N, int Q, int k, int sm_total, ScanCore* p) {
       if (eff >= 0.97 * best_eff) { best = s; break; }
     }
     S = best;
+    // A slice is read by all num_qt query tiles, on different units.  Nothing keeps those units in step, so over a
+    // 277 MB slice (10 M rows / 37) they drift further apart than L2 can hold and most of them fetch their rows from
+    // HBM on their own: ncu measured 136.6 GB of DRAM reads for a 10.24 GB store at Q = 10 000 (62 % L2 hit rate).
+    // Slices are therefore small -- everything in flight at one time, ceil(units / num_qt) consecutive slices, is a few
+    // MB -- and issued slice-major, so the units reading a slice are never more than a few slices apart.  Measured
+    // (profiles/r02_scan_c3_traffic.txt): 73-82 GB and 10 % less time; the hit rate stays near 72 % whatever the slice
+    // size (6-48 MB in flight) and whether or not the units are skewed against each other inside a slice, i.e. what is
+    // left is not a capacity effect (the missing step is a TMA-multicast cluster sharing each row tile).
+    const int conc = (sms + p->num_qt - 1) / p->num_qt;
+    int64_t inflight_mb = 12;
+    if (const char* e = getenv("EVR_SCAN_INFLIGHT_MB")) {   // tuning knob
+      if (atoi(e) > 0) inflight_mb = atoi(e);
+    }
+    int64_t target = (inflight_mb << 20) / conc;
+    if (target > (32ll << 20)) target = 32ll << 20;
+    if (target < (1ll << 20)) target = 1ll << 20;
+    int64_t tps = target / (static_cast<int64_t>(rowtile) * D * 2);
+    if (tps < 2) tps = 2;
+    const int64_t s_l2 = (tiles + tps - 1) / tps;
+    if (s_l2 > S) S = static_cast<int>(s_l2 < (1 << 20) ? s_l2 : (1 << 20));
   }
   p->tiles_per_slice = static_cast<int>((tiles + S - 1) / S);
   p->num_slices = static_cast<int>((tiles + p->tiles_per_slice - 1) / p->tiles_per_slice);
+  // candidate lists: one per slice while there are few; otherwise a ring that slice s shares with s - ring, s - 2 ring,
+  // ... (the kernel orders them with a flag per (32 queries, slice)); deep enough for the slices in flight plus drift
+  const int conc = p->num_qt > 1 ? (sms + p->num_qt - 1) / p->num_qt : p->num_slices;
+  int ring = 2 * conc + 6;
+  if (p->num_qt == 1 || ring > p->num_slices) ring = p->num_slices;
+  p->ring = ring;
   const long long items = static_cast<long long>(p->num_qt) * p->num_slices;
   p->grid = static_cast<int>(items < sms ? items : sms) * p->cg;
 }
@@ -875,22 +935,26 @@ static int plan_scan(int64_t N, int D, int Q, int k, ScanPlan* p) {
   EVR_REQUIRE(Q >= 1, "top-k scan: Q=%d", Q);
   EVR_REQUIRE(k >= 1 && k <= kMaxFusedK, "top-k scan: k=%d must be in [1, %d]", k, kMaxFusedK);
   const int sms = sm_count();
-  plan_core(N, Q, k, sms, &p->main);
-  EVR_REQUIRE(p->main.num_slices <= 256, "top-k scan: %d slices exceed the select kernel's limit", p->main.num_slices);
+  plan_core(N, D, Q, k, sms, &p->main);
+  EVR_REQUIRE(p->main.ring <= 256, "top-k scan: %d candidate lists per query exceed the select kernel's limit",
+              p->main.ring);
   p->n0 = sample_rows(N, k, Q);
   p->groups = static_cast<int>(p->n0 / 64);
   p->pre = ScanCore{};
-  if (p->n0 > 0) plan_core(p->n0, Q, k, sms, &p->pre);
-  const long long worst = static_cast<long long>(p->main.num_slices) * p->main.cap;
+  if (p->n0 > 0) plan_core(p->n0, D, Q, k, sms, &p->pre);
+  const long long worst = static_cast<long long>(p->main.ring) * p->main.cap;
   // shared-memory budget of the select kernel: everything at small query batch (one CTA per query, ~15 k
   // candidates), a few CTAs per SM at large batch; longer lists fall back to re-reading global memory
   const long long budget = Q <= 256 ? 24576 : 6144;
   p->select_cap = static_cast<int>(worst < budget ? worst : budget);
-  p->lists_bytes = up256(static_cast<size_t>(p->main.num_slices) * p->main.q_pad * p->main.cap * sizeof(int2));
-  p->counts_bytes = up256(static_cast<size_t>(p->main.num_slices) * p->main.q_pad * sizeof(int));
+  p->lists_bytes = up256(static_cast<size_t>(p->main.ring) * p->main.q_pad * p->main.cap * sizeof(int2));
+  p->counts_bytes = up256(static_cast<size_t>(p->main.ring) * p->main.q_pad * sizeof(int));
+  p->lthresh_bytes = up256(static_cast<size_t>(p->main.ring) * p->main.q_pad * sizeof(float));
+  p->done_bytes = up256(static_cast<size_t>(p->main.q_pad / 32) * p->main.num_slices * sizeof(unsigned));
   p->gmax_bytes = p->n0 > 0 ? up256(static_cast<size_t>(p->main.q_pad) * p->groups * sizeof(float)) : 0;
   p->thresh_bytes = up256(static_cast<size_t>(p->main.q_pad) * sizeof(float));
-  p->total_bytes = p->lists_bytes + p->counts_bytes + p->gmax_bytes + p->thresh_bytes + 256;
+  p->total_bytes = p->lists_bytes + p->counts_bytes + p->gmax_bytes + p->thresh_bytes + p->lthresh_bytes +
+                   p->done_bytes + 256;
   return 0;
 }
 
@@ -963,13 +1027,15 @@ extern "C" int evr_topk_workspace_bytes(int64_t N, int D, int Q, int k, size_t* 
 // in temporal order still yields a representative threshold; tile_stride = 1 and N_store = N for the full scan).
 static int run_scan(const ScanCore& c, const void* store, int64_t N, int64_t N_store, int tile_stride, int D,
                     const void* queries, int Q, int k, const float* init_thresh, int2* lists, int* counts,
-                    float* group_max, int groups, cudaStream_t s) {
+                    float* list_thresh, unsigned* done, unsigned epoch, float* group_max, int groups, cudaStream_t s) {
   ScanArgs a{};
   a.N = N; a.D = D; a.Q = Q; a.k = k; a.tile_stride = tile_stride;
+  { const char* e = getenv("EVR_SCAN_EVICT_LAST"); a.row_evict_last = (e && e[0] == '1' && c.num_qt > 1) ? 1 : 0; }
   a.num_qt = c.num_qt; a.num_slices = c.num_slices; a.tiles_per_slice = c.tiles_per_slice; a.q_pad = c.q_pad;
   a.cap = c.cap;
   a.init_thresh = init_thresh;
   a.lists = lists; a.counts = counts; a.group_max = group_max; a.groups = groups;
+  a.ring = c.ring; a.list_thresh = list_thresh; a.done = done; a.epoch = epoch;
   CUtensorMap tq, ts;
   if (int r = make_tmap_2d_16b(&tq, queries, Q, D, static_cast<uint64_t>(D) * 2, kScanQTile, false)) return r;
   if (int r = make_tmap_2d_16b(&ts, store, N_store, D, static_cast<uint64_t>(D) * 2, kScanRowTile, false)) return r;
@@ -1012,7 +1078,7 @@ extern "C" int evr_topk_search(const void* store, int64_t N, int D, int64_t row_
       if (e[0] == '1') stride = 1;
     }
     if (int r = run_scan(p.pre, store, p.n0, N, static_cast<int>(stride), D, queries, Q, k, nullptr, nullptr, nullptr,
-                         gmax, p.groups, s)) return r;
+                         nullptr, nullptr, 0u, gmax, p.groups, s)) return r;
     {
       ProfScope ps(PF_FINAL, s);
       sample_kth_kernel<<<(Q + 7) / 8, 256, 0, s>>>(gmax, p.groups, Q, k, thresh);
@@ -1020,10 +1086,17 @@ extern "C" int evr_topk_search(const void* store, int64_t N, int D, int64_t row_
     EVR_CHECK_LAUNCH();
     init = thresh;
   }
-  if (int r = run_scan(p.main, store, N, N, 1, D, queries, Q, k, init, lists, counts, nullptr, 0, s)) return r;
+  float* lthresh = reinterpret_cast<float*>(ws + p.lists_bytes + p.counts_bytes + p.gmax_bytes + p.thresh_bytes);
+  unsigned* done = reinterpret_cast<unsigned*>(ws + p.lists_bytes + p.counts_bytes + p.gmax_bytes + p.thresh_bytes +
+                                               p.lthresh_bytes);
+  static std::atomic<unsigned> epoch_counter{0};
+  unsigned epoch = epoch_counter.fetch_add(1, std::memory_order_relaxed) + 1;
+  if (epoch == 0) epoch = epoch_counter.fetch_add(1, std::memory_order_relaxed) + 1;   // 0 is what fresh memory holds
+  if (int r = run_scan(p.main, store, N, N, 1, D, queries, Q, k, init, lists, counts, lthresh, done, epoch, nullptr, 0,
+                       s)) return r;
   SelectArgs sa{};
   sa.lists = lists; sa.counts = counts;
-  sa.P = p.main.num_slices; sa.q_pad = p.main.q_pad; sa.cap = p.main.cap; sa.k = k; sa.smem_cap = p.select_cap;
+  sa.P = p.main.ring; sa.q_pad = p.main.q_pad; sa.cap = p.main.cap; sa.k = k; sa.smem_cap = p.select_cap;
   sa.row_offset = row_offset; sa.out_scores = out_scores; sa.out_idx = out_idx;
   int kp = 1;
   while (kp < k) kp <<= 1;
