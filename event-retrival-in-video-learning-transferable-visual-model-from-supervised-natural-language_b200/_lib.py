@@ -59,6 +59,13 @@ SIGNATURES = {
                                 ctypes.POINTER(c_void_p)]),
     "evr_text_destroy": (c_int, [c_void_p]),
     "evr_text_encode": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_void_p]),
+    "evr_jpeg_create": (c_int, [c_int, ctypes.POINTER(c_void_p)]),
+    "evr_jpeg_destroy": (c_int, [c_void_p]),
+    "evr_jpeg_backend": (c_int, [c_void_p]),
+    "evr_jpeg_info": (c_int, [c_void_p, c_void_p, c_size_t, ctypes.POINTER(c_int), ctypes.POINTER(c_int),
+                              ctypes.POINTER(c_int)]),
+    "evr_jpeg_decode_batch": (c_int, [c_void_p, ctypes.POINTER(c_void_p), ctypes.POINTER(c_size_t), c_int, c_int, c_int,
+                                      c_void_p, c_void_p]),
     "evr_attention": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "evr_gemm_bf16": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
 }

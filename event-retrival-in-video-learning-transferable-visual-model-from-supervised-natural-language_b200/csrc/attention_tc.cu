@@ -499,7 +499,6 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap128, const __grid_co
       const int b = item / a.heads, h = item - b * a.heads;
       const int st = it % a.stages;
       const uint32_t qs = smem_u32(smem + st * stage_bytes);
-      const uint32_t ks = qs + op_bytes;
       for (int j = 0; j < n_jobs; ++j, ++g) {
         if ((g & 1) != group) continue;
         const int n = g >> 1;

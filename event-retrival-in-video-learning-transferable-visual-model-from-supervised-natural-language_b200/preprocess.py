@@ -158,3 +158,63 @@ class GpuPreprocess:
                                              current_stream_ptr()), "evr_resize_crop_u8")
                 done += nb
         return out
+
+
+class JpegDecoder:
+    """JPEG files -> uint8 [B, H, W, 3] RGB frames in HBM through nvJPEG's batched decoder (`evr_jpeg_decode_batch`).
+
+    Replaces `Image.open(p).convert('RGB')` of the ingest loop (Backend/services/embedding_service.py:472-475) when the
+    service is created with `gpu_jpeg=True`.  The hardware JPEG engines are used when nvJPEG offers them for the stream
+    (single-scan baseline JPEGs, what `cv2.imwrite` writes for key-frames, segment_video.py:26); otherwise nvJPEG's GPU
+    Huffman path.  Pixels differ from libjpeg-turbo's by a few grey levels (IDCT / chroma up-sampling), so the `.npy`
+    rows are not bit-identical to the PIL path's: embeddings agree to cosine >= 0.999 (tests/test_jpeg_gpu.py)."""
+
+    def __init__(self, device="cuda", prefer_hardware=True):
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("JpegDecoder runs on a CUDA device only (the host path is PIL)")
+        self._h = ctypes.c_void_p()
+        with torch.cuda.device(self.device):
+            check(lib.evr_jpeg_create(1 if prefer_hardware else 0, ctypes.byref(self._h)), "evr_jpeg_create")
+        self.backend = {3: "hardware", 2: "gpu_hybrid", 0: "default"}.get(int(lib.evr_jpeg_backend(self._h)), "other")
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h:
+            try:
+                lib.evr_jpeg_destroy(h)
+            except Exception:
+                pass
+            self._h = None
+
+    def size(self, blob):
+        """(width, height) of one JPEG byte string, from its header."""
+        w, h, c = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+        buf = (ctypes.c_ubyte * len(blob)).from_buffer_copy(blob)
+        check(lib.evr_jpeg_info(self._h, buf, len(blob), ctypes.byref(w), ctypes.byref(h), ctypes.byref(c)),
+              "evr_jpeg_info")
+        return w.value, h.value
+
+    @torch.no_grad()
+    def decode(self, blobs, size=None):
+        """blobs: list of JPEG byte strings of ONE image size -> uint8 device tensor [B, H, W, 3]."""
+        n = len(blobs)
+        if n == 0:
+            return torch.empty((0, 0, 0, 3), dtype=torch.uint8, device=self.device)
+        W, H = size if size is not None else self.size(blobs[0])
+        keep = [(ctypes.c_ubyte * len(b)).from_buffer_copy(b) for b in blobs]
+        ptrs = (ctypes.c_void_p * n)(*[ctypes.addressof(k) for k in keep])
+        lens = (ctypes.c_size_t * n)(*[len(b) for b in blobs])
+        out = torch.empty((n, H, W, 3), dtype=torch.uint8, device=self.device)
+        with torch.cuda.device(self.device):
+            check(lib.evr_jpeg_decode_batch(self._h, ptrs, lens, n, H, W, ptr(out), current_stream_ptr()),
+                  "evr_jpeg_decode_batch")
+            torch.cuda.current_stream().synchronize()   # nvJPEG reads the host bytes asynchronously: keep them alive
+        return out
+
+    def decode_files(self, paths):
+        blobs = []
+        for p in paths:
+            with open(p, "rb") as f:
+                blobs.append(f.read())
+        return self.decode(blobs)

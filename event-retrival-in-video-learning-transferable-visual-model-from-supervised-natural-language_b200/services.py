@@ -348,11 +348,12 @@ class EmbeddingService:
     `clip`), `model_name`, `load_kwargs` (forwarded to clip.load, e.g. state_dict= / random_init=),
     `text_encoder` (callable str -> [1, D] array, used while the text tower is not built: SURVEY 8f row 1),
     `checkpoint_path` (fine-tuned CLIPWithClassifier checkpoint, embedding_service.py:93), `gpu_preprocess` (ingest
-    resizes/crops on the device, bit-identical to PIL; False keeps the per-frame host `preprocess`)."""
+    resizes/crops on the device, bit-identical to PIL; False keeps the per-frame host `preprocess`), `gpu_jpeg` (ingest
+    decodes `.jpg` files with nvJPEG on the device instead of PIL on host threads; default off / $EVR_GPU_JPEG)."""
 
     def __init__(self, cache_service, path_service, data_service, device="cuda", clip_module=None,
                  model_name="ViT-B/32", load_kwargs=None, text_encoder=None, checkpoint_path=None,
-                 gpu_preprocess=True):
+                 gpu_preprocess=True, gpu_jpeg=None):
         self.cache_service, self.path_service, self.data_service = cache_service, path_service, data_service
         self.device = device
         self._clip = clip_module or _clip
@@ -360,6 +361,9 @@ class EmbeddingService:
         self._load_kwargs = dict(load_kwargs or {})
         self.text_encoder = text_encoder
         self.gpu_preprocess = bool(gpu_preprocess)
+        # JPEG decode on the device (nvJPEG; preprocess.JpegDecoder): opt-in, because its pixels are not bit-identical
+        # to PIL's (embeddings agree to cosine >= 0.999); the default keeps the reference's own decoder
+        self.gpu_jpeg = bool(int(os.environ.get("EVR_GPU_JPEG", "0"))) if gpu_jpeg is None else bool(gpu_jpeg)
         self.decode_workers = None  # host threads decoding JPEGs during ingest (None: min(16, cores); 1: serial)
         self.original_model, self.preprocess = self._clip.load(model_name, device=device, **self._load_kwargs)
         self.finetuned_model = None
@@ -644,6 +648,8 @@ class EmbeddingService:
         all_embeddings, bad_rows = [], []
         if not frame_files:   # more ranks than frames
             return np.zeros((0, self.original_model.visual.output_dim), self._embedding_dtype(key)), bad_rows
+        if getattr(self.preprocess, "evr_n_px", None) == S and self.gpu_preprocess and self.gpu_jpeg:
+            return self._encode_frames_nvjpeg(folder_path, frame_files, key, S)
         if getattr(self.preprocess, "evr_n_px", None) == S and self.gpu_preprocess:
             # device path: PIL only decodes; Resize(bicubic) + CenterCrop run on the GPU bit-identically to PIL
             # (preprocess.py) and ToTensor + Normalize are fused into the encoder's im2col.  Frames of one size are
@@ -692,6 +698,96 @@ class EmbeddingService:
                         bad_rows.append(i + j)
                 all_embeddings.append(self._encode_images(torch.stack(batch).to(self.device), key))
         return np.vstack(all_embeddings), bad_rows
+
+    def _encode_frames_nvjpeg(self, folder_path, frame_files, key, S, batch=32, workers=2):
+        """The ingest loop with the JPEG decode on the device.  The sorted frame list is cut into runs of same-size
+        JPEGs (sizes from the headers); `workers` host threads, each with its own nvJPEG state and CUDA stream, read and
+        decode runs ahead of the consumer (nvJPEG's batched decode keeps one host thread busy parsing while its GPU
+        Huffman / IDCT kernels run, so several states in flight are what fills the device); the calling thread takes the
+        decoded runs in order: resize + crop (`GpuPreprocess`), tower, rows back.  A file nvJPEG cannot take (PNG,
+        progressive or damaged JPEG) goes through PIL for that frame; an undecodable frame is a zero row, as in the PIL
+        path."""
+        from PIL import Image
+        from ._lib import EvrError
+        from .preprocess import JpegDecoder
+        pre = self._gpu_pre = getattr(self, "_gpu_pre", None) or GpuPreprocess(S, self.device)
+        probe = self._jpeg = getattr(self, "_jpeg", None) or JpegDecoder(self.device)
+        pool_state = self._jpeg_workers = getattr(self, "_jpeg_workers", None) or threading.local()
+        rows = [None] * len(frame_files)
+        bad_rows = []
+        dev = torch.device(self.device)
+
+        def header_size(name):
+            if not name.lower().endswith(('.jpg', '.jpeg')):
+                return None
+            try:
+                with open(os.path.join(folder_path, name), "rb") as f:
+                    return probe.size(f.read(65536))     # the frame header sits in the first KBs
+            except (EvrError, OSError):
+                return None
+
+        def via_pil(i):
+            try:
+                frame = np.array(Image.open(os.path.join(folder_path, frame_files[i])).convert('RGB'))
+                rows[i] = self._encode_images(pre(frame), key)[0]
+            except Exception as e:
+                print(f"Error preprocessing image {frame_files[i]}: {e}")
+                bad_rows.append(i)
+
+        def decode_run(run):
+            """worker thread: files of one run -> (device frames, event on the worker's stream) or None"""
+            idx, size = run
+            if size is None:
+                return None
+            if not hasattr(pool_state, "dec"):
+                pool_state.dec = JpegDecoder(dev)
+                pool_state.stream = torch.cuda.Stream(device=dev)
+            blobs = []
+            for i in idx:
+                with open(os.path.join(folder_path, frame_files[i]), "rb") as f:
+                    blobs.append(f.read())
+            try:
+                with torch.cuda.device(dev), torch.cuda.stream(pool_state.stream):
+                    frames = pool_state.dec.decode(blobs, size)
+                    done = torch.cuda.Event()
+                    done.record(pool_state.stream)
+                return frames, done
+            except EvrError:
+                return None
+
+        # runs of consecutive same-size JPEGs, at most `batch` long; anything else is a run of one with size None
+        with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1)) as pool:
+            sizes = list(pool.map(header_size, frame_files))
+        runs = []
+        for i, size in enumerate(sizes):
+            if size is not None and runs and runs[-1][1] == size and len(runs[-1][0]) < batch:
+                runs[-1][0].append(i)
+            else:
+                runs.append(([i], size))
+        with ThreadPoolExecutor(max_workers=workers) as pool:
+            pending, nxt = deque(), 0
+            while nxt < len(runs) or pending:
+                while nxt < len(runs) and len(pending) < workers + 1:
+                    pending.append((runs[nxt], pool.submit(decode_run, runs[nxt])))
+                    nxt += 1
+                (idx, _), fut = pending.popleft()
+                res = fut.result()
+                if res is None:            # not a baseline JPEG (or one of the run is not): frame by frame through PIL
+                    for i in idx:
+                        via_pil(i)
+                    continue
+                frames, done = res
+                torch.cuda.current_stream(dev).wait_event(done)
+                frames.record_stream(torch.cuda.current_stream(dev))
+                emb = self._encode_images(pre(frames), key)
+                for i, row in zip(idx, emb):
+                    rows[i] = row
+        D = self.original_model.visual.output_dim
+        out = np.zeros((len(frame_files), D), self._embedding_dtype(key))
+        for i, row in enumerate(rows):
+            if row is not None:
+                out[i] = row
+        return out, sorted(bad_rows)
 
     def _stamp_metadata(self, video_name, model_key):
         """:509-526 -- record which model produced the store in the video's metadata JSON."""

@@ -165,6 +165,19 @@ int evr_text_encode(evr_text* h, const int32_t* tokens, int B, void* out, int ou
 int evr_gemm_bf16(const void* A, const void* W, const float* bias, void* out, int M, int N, int K, int epilogue,
                   void* stream);
 
+/* ---- JPEG key-frames decoded on the device (nvJPEG batched decode; hardware engines when the stream allows) ------
+ * replaces  Image.open(path).convert('RGB')   Backend/services/embedding_service.py:472-475, Backend/embedding.py:45
+ * data[i] / lengths[i]: the i-th file's bytes in HOST memory; every image of a batch has the same H x W;
+ * dst: DEVICE [n, H, W, 3] uint8 RGB (what evr_resize_crop_u8 takes).  Not bit-identical to libjpeg-turbo / PIL
+ * (IDCT and chroma up-sampling differ): opt-in, parity stated on the embeddings (cosine >= 0.999). */
+typedef struct evr_jpeg evr_jpeg;
+int evr_jpeg_create(int prefer_hardware, evr_jpeg** out);
+int evr_jpeg_destroy(evr_jpeg* h);
+int evr_jpeg_backend(const evr_jpeg* h); /* nvjpegBackend_t in use: 3 = hardware engine, 2 = GPU hybrid, 0 = default */
+int evr_jpeg_info(evr_jpeg* h, const uint8_t* data, size_t length, int* width, int* height, int* components);
+int evr_jpeg_decode_batch(evr_jpeg* h, const uint8_t* const* data, const size_t* lengths, int n, int H, int W,
+                          uint8_t* dst, void* stream);
+
 /* building-block attention core exported for the parity tests: softmax(q k^T / 8 [+ causal mask]) v per
  * (sequence, head), head dim 64.  qkv bf16 [B L, 3 d] (q | k | v as the in_proj GEMM writes it), out bf16 [B L, d].
  * impl 0: what the towers use (tcgen05 / TMEM for 64 < L <= 257, warp-level MMA otherwise), 1: warp-level MMA kernels,
