@@ -10,7 +10,7 @@ OpenAI weights are on this box => PARITY UNPINNED at the clip.encode_image bound
 the reference's own artefacts.  This file restates the published algorithm of
 clip/model.py (LayerNorm-in-fp32, QuickGELU, ResidualAttentionBlock, Transformer,
 VisionTransformer, CLIP.encode_image) with openai-compatible state_dict keys and is
-cross-checked against transformers.CLIPVisionModelWithProjection (tests/test_oracle.py).
+cross-checked against transformers.CLIPVisionModelWithProjection (tests/test_oracle_vit.py).
 """
 import math
 from collections import OrderedDict
