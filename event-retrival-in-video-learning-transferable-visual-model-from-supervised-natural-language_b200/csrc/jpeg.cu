@@ -8,12 +8,71 @@
 // embeddings (cosine >= 0.999 against the PIL-decoded path, tests/test_jpeg_gpu.py); PIL stays the exact mode.
 #include <nvjpeg.h>
 
+#include <atomic>
+#include <cstdlib>
+#include <mutex>
+#include <unordered_map>
 #include <vector>
 
 #include "../../include/evr.h"
 #include "common.cuh"
 
 using namespace evr;
+
+// nvJPEG allocates and frees its work buffers around every batched call; with the default allocators that is a
+// cudaMalloc / cudaFree (a device-wide synchronisation) per call, ~20 ms per batch whatever its size.  These pools
+// hand the same blocks back: power-of-two buckets, kept until the last decoder is destroyed.
+namespace {
+struct BlockPool {
+  std::mutex mu;
+  std::unordered_map<void*, size_t> bucket_of;             // every block ever handed out -> its bucket size
+  std::unordered_map<size_t, std::vector<void*>> free_list;
+  bool pinned;
+  explicit BlockPool(bool pin) : pinned(pin) {}
+  static size_t bucket(size_t n) {
+    size_t b = 4096;
+    while (b < n) b <<= 1;
+    return b;
+  }
+  int get(void** p, size_t n) {
+    const size_t b = bucket(n);
+    std::lock_guard<std::mutex> g(mu);
+    auto& fl = free_list[b];
+    if (!fl.empty()) {
+      *p = fl.back();
+      fl.pop_back();
+      return 0;
+    }
+    cudaError_t e = pinned ? cudaMallocHost(p, b) : cudaMalloc(p, b);
+    if (e != cudaSuccess) return 1;
+    bucket_of[*p] = b;
+    return 0;
+  }
+  int put(void* p) {
+    if (!p) return 0;
+    std::lock_guard<std::mutex> g(mu);
+    auto it = bucket_of.find(p);
+    if (it == bucket_of.end()) return 1;
+    free_list[it->second].push_back(p);
+    return 0;
+  }
+  void release() {
+    std::lock_guard<std::mutex> g(mu);
+    for (auto& kv : free_list)
+      for (void* p : kv.second) {
+        if (pinned) cudaFreeHost(p); else cudaFree(p);
+        bucket_of.erase(p);
+      }
+    free_list.clear();
+  }
+};
+BlockPool g_dev_pool(false), g_pin_pool(true);
+std::atomic<int> g_decoders{0};
+int dev_malloc(void** p, size_t n) { return g_dev_pool.get(p, n); }
+int dev_free(void* p) { return g_dev_pool.put(p); }
+int pin_malloc(void** p, size_t n, unsigned int) { return g_pin_pool.get(p, n); }
+int pin_free(void* p) { return g_pin_pool.put(p); }
+}  // namespace
 
 struct evr_jpeg {
   nvjpegHandle_t handle = nullptr;
@@ -35,16 +94,20 @@ extern "C" int evr_jpeg_create(int prefer_hardware, evr_jpeg** out) {
   EVR_REQUIRE(out, "evr_jpeg_create: null out");
   evr_jpeg* h = new evr_jpeg();
   nvjpegStatus_t st = NVJPEG_STATUS_NOT_INITIALIZED;
+  static nvjpegDevAllocator_t dev_alloc = {dev_malloc, dev_free};       // nvJPEG may keep the pointers
+  static nvjpegPinnedAllocator_t pin_alloc = {pin_malloc, pin_free};
+  nvjpegDevAllocator_t* da = getenv("EVR_JPEG_NO_POOL") ? nullptr : &dev_alloc;
+  nvjpegPinnedAllocator_t* pa = getenv("EVR_JPEG_NO_POOL") ? nullptr : &pin_alloc;
   if (prefer_hardware) {
-    st = nvjpegCreateEx(NVJPEG_BACKEND_HARDWARE, nullptr, nullptr, NVJPEG_FLAGS_DEFAULT, &h->handle);
+    st = nvjpegCreateEx(NVJPEG_BACKEND_HARDWARE, da, pa, NVJPEG_FLAGS_DEFAULT, &h->handle);
     if (st == NVJPEG_STATUS_SUCCESS) h->backend = NVJPEG_BACKEND_HARDWARE;
   }
   if (st != NVJPEG_STATUS_SUCCESS) {
-    st = nvjpegCreateEx(NVJPEG_BACKEND_GPU_HYBRID, nullptr, nullptr, NVJPEG_FLAGS_DEFAULT, &h->handle);
+    st = nvjpegCreateEx(NVJPEG_BACKEND_GPU_HYBRID, da, pa, NVJPEG_FLAGS_DEFAULT, &h->handle);
     if (st == NVJPEG_STATUS_SUCCESS) h->backend = NVJPEG_BACKEND_GPU_HYBRID;
   }
   if (st != NVJPEG_STATUS_SUCCESS) {
-    st = nvjpegCreateSimple(&h->handle);
+    st = nvjpegCreateEx(NVJPEG_BACKEND_DEFAULT, da, pa, NVJPEG_FLAGS_DEFAULT, &h->handle);
     h->backend = NVJPEG_BACKEND_DEFAULT;
   }
   if (st != NVJPEG_STATUS_SUCCESS) {
@@ -58,6 +121,7 @@ extern "C" int evr_jpeg_create(int prefer_hardware, evr_jpeg** out) {
     evr::set_error("evr_jpeg_create: nvjpegJpegStateCreate failed");
     return 1;
   }
+  g_decoders.fetch_add(1);
   *out = h;
   return 0;
 }
@@ -69,6 +133,10 @@ extern "C" int evr_jpeg_destroy(evr_jpeg* h) {
   if (h->state) nvjpegJpegStateDestroy(h->state);
   if (h->handle) nvjpegDestroy(h->handle);
   delete h;
+  if (g_decoders.fetch_sub(1) == 1) {   // last decoder gone: give the pooled blocks back
+    g_dev_pool.release();
+    g_pin_pool.release();
+  }
   return 0;
 }
 
@@ -96,7 +164,9 @@ extern "C" int evr_jpeg_decode_batch(evr_jpeg* h, const uint8_t* const* data, co
     EVR_REQUIRE(w[0] == W && hh[0] == H, "evr_jpeg_decode_batch: image %d is %dx%d, batch is %dx%d", i, w[0], hh[0], W, H);
   }
   if (h->batch != n) {
-    EVR_CHECK_NVJPEG(nvjpegDecodeBatchedInitialize(h->handle, h->state, n, 1, NVJPEG_OUTPUT_RGBI));
+    int threads = 1;   // host threads nvJPEG may use for the parts it keeps on the CPU (EVR_JPEG_THREADS: experiments)
+    if (const char* e = getenv("EVR_JPEG_THREADS")) threads = atoi(e) > 0 ? atoi(e) : 1;
+    EVR_CHECK_NVJPEG(nvjpegDecodeBatchedInitialize(h->handle, h->state, n, threads, NVJPEG_OUTPUT_RGBI));
     h->batch = n;
   }
   std::vector<nvjpegImage_t> outs(n);

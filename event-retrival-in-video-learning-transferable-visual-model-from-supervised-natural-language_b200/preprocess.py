@@ -160,6 +160,33 @@ class GpuPreprocess:
         return out
 
 
+def jpeg_frame_size(blob):
+    """(width, height) from the SOF0 / SOF1 header of a baseline JPEG byte string, None for anything else (progressive,
+    lossless, arithmetic-coded, not a JPEG): those go through PIL.  A marker walk over the first segments only."""
+    n = len(blob)
+    if n < 4 or blob[0] != 0xFF or blob[1] != 0xD8:
+        return None
+    i = 2
+    while i + 9 < n:
+        if blob[i] != 0xFF:
+            return None
+        m = blob[i + 1]
+        if m == 0xFF:                    # fill byte
+            i += 1
+            continue
+        if m in (0xC0, 0xC1):            # baseline / extended sequential, Huffman
+            return (blob[i + 7] << 8) | blob[i + 8], (blob[i + 5] << 8) | blob[i + 6]
+        if 0xC2 <= m <= 0xCF and m not in (0xC4, 0xC8, 0xCC):
+            return None                  # any other start-of-frame
+        if m == 0xDA or m == 0xD9:       # scan data before a frame header
+            return None
+        if 0xD0 <= m <= 0xD7 or m == 0x01:
+            i += 2
+            continue
+        i += 2 + ((blob[i + 2] << 8) | blob[i + 3])
+    return None
+
+
 class JpegDecoder:
     """JPEG files -> uint8 [B, H, W, 3] RGB frames in HBM through nvJPEG's batched decoder (`evr_jpeg_decode_batch`).
 
@@ -202,8 +229,8 @@ class JpegDecoder:
         if n == 0:
             return torch.empty((0, 0, 0, 3), dtype=torch.uint8, device=self.device)
         W, H = size if size is not None else self.size(blobs[0])
-        keep = [(ctypes.c_ubyte * len(b)).from_buffer_copy(b) for b in blobs]
-        ptrs = (ctypes.c_void_p * n)(*[ctypes.addressof(k) for k in keep])
+        keep = [b if isinstance(b, bytes) else bytes(b) for b in blobs]      # read in place, alive until the sync below
+        ptrs = (ctypes.c_void_p * n)(*[ctypes.cast(ctypes.c_char_p(b), ctypes.c_void_p).value for b in keep])
         lens = (ctypes.c_size_t * n)(*[len(b) for b in blobs])
         out = torch.empty((n, H, W, 3), dtype=torch.uint8, device=self.device)
         with torch.cuda.device(self.device):

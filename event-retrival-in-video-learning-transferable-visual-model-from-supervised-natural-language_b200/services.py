@@ -699,32 +699,24 @@ class EmbeddingService:
                 all_embeddings.append(self._encode_images(torch.stack(batch).to(self.device), key))
         return np.vstack(all_embeddings), bad_rows
 
-    def _encode_frames_nvjpeg(self, folder_path, frame_files, key, S, batch=32, workers=2):
-        """The ingest loop with the JPEG decode on the device.  The sorted frame list is cut into runs of same-size
-        JPEGs (sizes from the headers); `workers` host threads, each with its own nvJPEG state and CUDA stream, read and
-        decode runs ahead of the consumer (nvJPEG's batched decode keeps one host thread busy parsing while its GPU
-        Huffman / IDCT kernels run, so several states in flight are what fills the device); the calling thread takes the
-        decoded runs in order: resize + crop (`GpuPreprocess`), tower, rows back.  A file nvJPEG cannot take (PNG,
-        progressive or damaged JPEG) goes through PIL for that frame; an undecodable frame is a zero row, as in the PIL
-        path."""
+    def _encode_frames_nvjpeg(self, folder_path, frame_files, key, S, batch=256, workers=3):
+        """The ingest loop with the JPEG decode on the device.  The sorted frame list is cut into runs of `batch` files;
+        `workers` host threads, each with its own nvJPEG state and CUDA stream, read a run, split it into segments of
+        same-size baseline JPEGs (sizes from the SOF headers) and decode each segment with one batched call, ahead of
+        the consumer.  nvJPEG's batched decode costs ~20 ms per call almost independently of the batch (its GPU Huffman
+        stage is a few long sequential chains per image), so the batches are large (256 frames of 720p = 0.7 GB of RGB)
+        and several are in flight.  The calling thread takes the decoded segments in order: resize + crop
+        (`GpuPreprocess`), tower, rows back.  A file nvJPEG cannot take (PNG, progressive or damaged JPEG) goes through
+        PIL for that frame; an undecodable frame is a zero row, as in the PIL path."""
         from PIL import Image
         from ._lib import EvrError
-        from .preprocess import JpegDecoder
+        from .preprocess import JpegDecoder, jpeg_frame_size
         pre = self._gpu_pre = getattr(self, "_gpu_pre", None) or GpuPreprocess(S, self.device)
-        probe = self._jpeg = getattr(self, "_jpeg", None) or JpegDecoder(self.device)
+        self._jpeg = getattr(self, "_jpeg", None) or JpegDecoder(self.device)
         pool_state = self._jpeg_workers = getattr(self, "_jpeg_workers", None) or threading.local()
         rows = [None] * len(frame_files)
         bad_rows = []
         dev = torch.device(self.device)
-
-        def header_size(name):
-            if not name.lower().endswith(('.jpg', '.jpeg')):
-                return None
-            try:
-                with open(os.path.join(folder_path, name), "rb") as f:
-                    return probe.size(f.read(65536))     # the frame header sits in the first KBs
-            except (EvrError, OSError):
-                return None
 
         def via_pil(i):
             try:
@@ -734,54 +726,59 @@ class EmbeddingService:
                 print(f"Error preprocessing image {frame_files[i]}: {e}")
                 bad_rows.append(i)
 
-        def decode_run(run):
-            """worker thread: files of one run -> (device frames, event on the worker's stream) or None"""
-            idx, size = run
-            if size is None:
-                return None
+        def decode_run(idx):
+            """worker thread: files of one run -> [(indices, device frames | None, event | None)] in file order"""
             if not hasattr(pool_state, "dec"):
                 pool_state.dec = JpegDecoder(dev)
                 pool_state.stream = torch.cuda.Stream(device=dev)
-            blobs = []
+            segments = []           # [indices, size, blobs]
             for i in idx:
-                with open(os.path.join(folder_path, frame_files[i]), "rb") as f:
-                    blobs.append(f.read())
-            try:
-                with torch.cuda.device(dev), torch.cuda.stream(pool_state.stream):
-                    frames = pool_state.dec.decode(blobs, size)
-                    done = torch.cuda.Event()
-                    done.record(pool_state.stream)
-                return frames, done
-            except EvrError:
-                return None
+                blob, size = None, None
+                if frame_files[i].lower().endswith(('.jpg', '.jpeg')):
+                    try:
+                        with open(os.path.join(folder_path, frame_files[i]), "rb") as f:
+                            blob = f.read()
+                        size = jpeg_frame_size(blob)     # None: not a baseline JPEG
+                    except OSError:
+                        size = None
+                if size is not None and segments and segments[-1][1] == size:
+                    segments[-1][0].append(i)
+                    segments[-1][2].append(blob)
+                else:
+                    segments.append([[i], size, [blob]])
+            out = []
+            for seg_idx, size, blobs in segments:
+                if size is None:
+                    out.append((seg_idx, None, None))
+                    continue
+                try:
+                    with torch.cuda.device(dev), torch.cuda.stream(pool_state.stream):
+                        frames = pool_state.dec.decode(blobs, size)
+                        done = torch.cuda.Event()
+                        done.record(pool_state.stream)
+                    out.append((seg_idx, frames, done))
+                except EvrError:
+                    out.append((seg_idx, None, None))
+            return out
 
-        # runs of consecutive same-size JPEGs, at most `batch` long; anything else is a run of one with size None
-        with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1)) as pool:
-            sizes = list(pool.map(header_size, frame_files))
-        runs = []
-        for i, size in enumerate(sizes):
-            if size is not None and runs and runs[-1][1] == size and len(runs[-1][0]) < batch:
-                runs[-1][0].append(i)
-            else:
-                runs.append(([i], size))
+        runs = [list(range(i, min(i + batch, len(frame_files)))) for i in range(0, len(frame_files), batch)]
         with ThreadPoolExecutor(max_workers=workers) as pool:
             pending, nxt = deque(), 0
             while nxt < len(runs) or pending:
-                while nxt < len(runs) and len(pending) < workers + 1:
-                    pending.append((runs[nxt], pool.submit(decode_run, runs[nxt])))
+                while nxt < len(runs) and len(pending) < workers:
+                    pending.append(pool.submit(decode_run, runs[nxt]))
                     nxt += 1
-                (idx, _), fut = pending.popleft()
-                res = fut.result()
-                if res is None:            # not a baseline JPEG (or one of the run is not): frame by frame through PIL
-                    for i in idx:
-                        via_pil(i)
-                    continue
-                frames, done = res
-                torch.cuda.current_stream(dev).wait_event(done)
-                frames.record_stream(torch.cuda.current_stream(dev))
-                emb = self._encode_images(pre(frames), key)
-                for i, row in zip(idx, emb):
-                    rows[i] = row
+                for idx, frames, done in pending.popleft().result():
+                    if frames is None:     # not a baseline JPEG (or one of the segment is not): frame by frame via PIL
+                        for i in idx:
+                            via_pil(i)
+                        continue
+                    torch.cuda.current_stream(dev).wait_event(done)
+                    frames.record_stream(torch.cuda.current_stream(dev))
+                    emb = self._encode_images(pre(frames), key)
+                    for i, row in zip(idx, emb):
+                        rows[i] = row
+                    del frames
         D = self.original_model.visual.output_dim
         out = np.zeros((len(frame_files), D), self._embedding_dtype(key))
         for i, row in enumerate(rows):

@@ -36,7 +36,7 @@ def run(n_frames=1024, quiet=False):
                                       os.path.join(tmp, "embedding"))
         cs = pkg.services.CacheService()
         svc = pkg.services.EmbeddingService(cs, ps, pkg.services.DataService(ps, cs), "cuda",
-                                            load_kwargs=dict(state_dict=sd, max_batch=64), gpu_jpeg=mode)
+                                            load_kwargs=dict(state_dict=sd, max_batch=256), gpu_jpeg=mode)
         svc.extract_and_save_embeddings_from_folder(folder, None, "warm")          # warm-up pass (pinned buffers, plans)
         t0 = time.perf_counter()
         path = svc.extract_and_save_embeddings_from_folder(folder, None, "vid")

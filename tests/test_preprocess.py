@@ -1,6 +1,7 @@
 """Preprocessing tables + integer arithmetic against PIL itself (CPU): clip._transform's Resize(224, BICUBIC) +
 CenterCrop(224) must be reproduced bit for bit (the CUDA kernels perform exactly `resample_reference_u8`)."""
 import importlib
+import os
 
 import numpy as np
 import pytest
@@ -44,3 +45,29 @@ def test_stretch_mode_equals_torchvision_resize(h, w):
     assert np.array_equal(po.pil_stretch_u8(img, 224), out)
     with pytest.raises(ValueError):
         pp.plan(w, h, 224, "nearest")
+
+
+def test_jpeg_frame_size_reads_sof_headers():
+    """`jpeg_frame_size` (the run splitter of the nvJPEG ingest path) against PIL on the reference's own key-frames,
+    plus the streams that must be refused (progressive, PNG, truncated)."""
+    import io
+    import importlib
+    from PIL import Image
+    from conftest import PKG
+    size = importlib.import_module(PKG + ".preprocess").jpeg_frame_size
+    d = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_frames")
+    names = sorted(f for f in os.listdir(d) if f.endswith(".jpg"))
+    assert names
+    for n in names:
+        blob = open(os.path.join(d, n), "rb").read()
+        assert size(blob) == Image.open(io.BytesIO(blob)).size
+    img = Image.fromarray((np.arange(96 * 160 * 3) % 251).astype(np.uint8).reshape(96, 160, 3))
+    for kw, expect in ((dict(), (160, 96)), (dict(optimize=True, quality=40), (160, 96)),
+                       (dict(progressive=True), None)):
+        buf = io.BytesIO()
+        img.save(buf, "JPEG", **kw)
+        assert size(buf.getvalue()) == expect, kw
+    buf = io.BytesIO()
+    img.save(buf, "PNG")
+    assert size(buf.getvalue()) is None
+    assert size(b"") is None and size(b"\xff\xd8\xff") is None and size(blob[:12]) is None
