@@ -199,6 +199,29 @@ def lists_agree(torch, s_a, i_a, s_b, i_b, eps):
     return bool(ok.all())
 
 
+def timeline_breakdown(timeline, batches):
+    """Device-stamped (family, start, end) of one step -> ms per batch: busy time per family, the time no stamped kernel
+    was running (launch gaps + the few unstamped small kernels), and how much neighbours overlapped (PDL)."""
+    if not timeline:
+        return None
+    busy, overlap, idle = {}, 0, 0
+    ordered = sorted(timeline, key=lambda t: t[1])
+    frontier = ordered[0][1]
+    for fam, t0, t1 in ordered:
+        busy[fam] = busy.get(fam, 0) + (t1 - t0)
+        if t0 > frontier:
+            idle += t0 - frontier
+        else:
+            overlap += min(frontier, t1) - t0
+        frontier = max(frontier, t1)
+    span = frontier - ordered[0][1]
+    out = {f: round(v * 1e-6 / batches, 4) for f, v in busy.items()}
+    out.update(idle_between_kernels=round(idle * 1e-6 / batches, 4), overlapped=round(overlap * 1e-6 / batches, 4),
+               span=round(span * 1e-6 / batches, 4), launches_per_batch=round(len(ordered) / batches, 1),
+               avg_us={f: round(busy[f] * 1e-3 / sum(1 for t in ordered if t[0] == f), 2) for f in busy})
+    return out
+
+
 # ----------------------------------------------------------------------------------------------- secondary legs
 def bench_encode_other(pkg, dev, name, batch, steps, warmup, peaks):
     """Secondary line: another tower geometry (BASELINE config 5 is ViT-L/14) on rank 0's GPU, device-resident frames."""
@@ -396,7 +419,10 @@ def bench_ingest_jpeg(pkg, dev, peaks, n_frames=4096, pil_sample=512):
                          "gpu_launches": pkg._lib.launch_count() - launches0}
             if mode:
                 out[mode]["backend"] = svc._jpeg.backend
-        a, b = rows[False], rows[True][:pil_sample]
+        # rows follow sorted(os.listdir(folder)) (embedding_service.py:452): align the two folders by file name
+        where = {name: i for i, name in enumerate(sorted(f"{i}.jpg" for i in range(n_frames)))}
+        a = rows[False]
+        b = rows[True][[where[name] for name in sorted(f"{i}.jpg" for i in range(pil_sample))]]
         cos = (a * b).sum(-1) / (np.linalg.norm(a, axis=-1) * np.linalg.norm(b, axis=-1))
     finally:
         shutil.rmtree(tmp, ignore_errors=True)
@@ -594,6 +620,7 @@ def bench_encode(pkg, dev, rank, world, steps, warmup, batch, inner, peaks):
         one_step(0)
         torch.cuda.synchronize()
         dt_ms, dt_n = _lib.profile_read()["gemm_tc"]
+        in_situ = timeline_breakdown(_lib.profile_timeline(), inner)
         # pass B, CUDA events around every launch: per-family split (serialises the overlap, +~5 us per launch)
         _lib.profile_enable(True)
         one_step(0)
@@ -622,6 +649,7 @@ def bench_encode(pkg, dev, rank, world, steps, warmup, batch, inner, peaks):
             "share_of_step": round((dt_ms if dt_n else gemm_ms) / step_ms, 4),
             "whole_step_frac": round(whole / peaks["tf_sustained"], 4), "whole_step_tflops": round(whole, 1),
             "whole_step_frac_of_burst_peak": round(whole / peaks["tf_burst"], 4),
+            "in_situ_ms_per_batch": in_situ,
             "event_timed": {"achieved": round(ev_ach, 1), "frac": round(ev_ach / peaks["tf_sustained"], 4),
                             "family_ms_per_batch": {k: round(v[0] / inner, 4) for k, v in fam.items() if v[1]},
                             "share_of_step": round(gemm_ms / all_ms, 4),

@@ -37,6 +37,8 @@ SIGNATURES = {
     "evr_launch_count": (c_int64, []),
     "evr_profile_enable": (c_int, [c_int]),
     "evr_profile_read": (c_int, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(c_int64), c_int]),
+    "evr_profile_timeline": (c_int, [ctypes.POINTER(ctypes.c_uint64), ctypes.POINTER(c_int), c_int,
+                                     ctypes.POINTER(c_int)]),
     "evr_store_prepare": (c_int, [c_void_p, c_int, c_int64, c_int, c_void_p, c_void_p]),
     "evr_topk_workspace_bytes": (c_int, [c_int64, c_int, c_int, c_int, ctypes.POINTER(c_size_t)]),
     "evr_topk_search": (c_int, [c_void_p, c_int64, c_int, c_int64, c_void_p, c_int, c_int, c_void_p, c_void_p,
@@ -66,6 +68,7 @@ SIGNATURES = {
                               ctypes.POINTER(c_int)]),
     "evr_jpeg_decode_batch": (c_int, [c_void_p, ctypes.POINTER(c_void_p), ctypes.POINTER(c_size_t), c_int, c_int, c_int,
                                       c_void_p, c_void_p]),
+    "evr_layernorm": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int, c_void_p, c_void_p, c_int, c_int, c_void_p]),
     "evr_attention": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "evr_gemm_bf16": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
 }
@@ -88,8 +91,8 @@ PROFILE_FAMILIES = ("gemm_tc", "attention", "layernorm", "vit_misc", "topk_scan"
 
 
 def profile_enable(on):
-    """True / 1: CUDA events around every launch (all families).  2: no events, the GEMM kernel stamps %globaltimer
-    itself (its launches timed in place, PDL overlap intact).  False / 0: off."""
+    """True / 1: CUDA events around every launch (all families).  2: no events, the GEMM / LayerNorm / attention
+    kernels stamp %globaltimer themselves (timed in place, PDL overlap intact).  False / 0: off."""
     check(lib.evr_profile_enable(2 if on == 2 else (1 if on else 0)), "evr_profile_enable")
 
 
@@ -100,6 +103,16 @@ def profile_read():
     cnt = (c_int64 * n)()
     check(lib.evr_profile_read(ms, cnt, n), "evr_profile_read")
     return {f: (ms[i], int(cnt[i])) for i, f in enumerate(PROFILE_FAMILIES)}
+
+
+def profile_timeline(capacity=16384):
+    """After profile_enable(2) and some launches: [(family, start_ns, end_ns)] in launch order (%globaltimer)."""
+    se = (ctypes.c_uint64 * (2 * capacity))()
+    fam = (c_int * capacity)()
+    n = c_int(0)
+    check(lib.evr_profile_timeline(se, fam, capacity, ctypes.byref(n)), "evr_profile_timeline")
+    return [(PROFILE_FAMILIES[fam[i]], int(se[2 * i]), int(se[2 * i + 1])) for i in range(n.value)
+            if se[2 * i + 1] > se[2 * i]]
 
 
 def current_stream_ptr():

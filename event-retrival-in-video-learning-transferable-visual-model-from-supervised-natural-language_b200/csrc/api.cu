@@ -57,6 +57,28 @@ int make_tmap_2d_16b(CUtensorMap* out, const void* base, uint64_t rows, uint64_t
   return 0;
 }
 
+// [batches][rows][cols] view of a packed activation: a box of `box_rows` rows never crosses into the next batch entry --
+// rows past `rows` are out of bounds in their own dimension and arrive as zeros.
+int make_tmap_3d_16b(CUtensorMap* out, const void* base, uint64_t batches, uint64_t rows, uint64_t cols,
+                     uint64_t row_stride_bytes, uint32_t box_rows, bool is_bf16) {
+  encode_tiled_fn enc = get_encode();
+  EVR_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled not available from the driver");
+  EVR_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "tensor base %p not 16-B aligned", base);
+  EVR_REQUIRE(row_stride_bytes % 16 == 0, "row stride %llu not a multiple of 16 B",
+              (unsigned long long)row_stride_bytes);
+  EVR_REQUIRE(box_rows >= 1 && box_rows <= 256, "TMA box rows %u out of range", box_rows);
+  cuuint64_t dims[3] = {cols, rows, batches};
+  cuuint64_t strides[2] = {row_stride_bytes, row_stride_bytes * rows};
+  cuuint32_t box[3] = {64, box_rows, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(out, is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3,
+                   const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  EVR_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (3-D) failed: CUresult %d (batches %llu rows %llu cols %llu)",
+              (int)r, (unsigned long long)batches, (unsigned long long)rows, (unsigned long long)cols);
+  return 0;
+}
+
 int sm_count() {
   static int cached[64] = {};
   int dev = 0;
@@ -171,10 +193,13 @@ void prof_end(void* token, cudaStream_t s) {
 static constexpr int kProfSlots = 16384;
 static unsigned long long* g_dt_pool = nullptr;
 static std::atomic<int> g_dt_used{0};
-unsigned long long* prof_device_slot() {
+static uint8_t g_dt_family[kProfSlots];
+unsigned long long* prof_device_slot(int family) {
   if (g_profile_on.load(std::memory_order_relaxed) != 2 || g_dt_pool == nullptr) return nullptr;
   const int i = g_dt_used.fetch_add(1, std::memory_order_relaxed);
-  return i < kProfSlots ? g_dt_pool + 2 * i : nullptr;
+  if (i >= kProfSlots) return nullptr;
+  g_dt_family[i] = static_cast<uint8_t>(family);
+  return g_dt_pool + 2 * i;
 }
 static int prof_device_reset() {
   if (g_dt_pool == nullptr) EVR_CHECK_CUDA(cudaMalloc(&g_dt_pool, 2 * kProfSlots * sizeof(unsigned long long)));
@@ -207,6 +232,19 @@ int evr_profile_enable(int on) {
   evr::g_profile_on.store(on == 2 ? 2 : (on ? 1 : 0));
   return 0;
 }
+int evr_profile_timeline(uint64_t* start_end_ns, int* family, int capacity, int* count) {
+  EVR_REQUIRE(start_end_ns && family && count, "evr_profile_timeline: null argument");
+  int used = evr::g_dt_used.load() < evr::kProfSlots ? evr::g_dt_used.load() : evr::kProfSlots;
+  if (used > capacity) used = capacity;
+  *count = 0;
+  if (evr::g_dt_pool == nullptr || used <= 0) return 0;
+  EVR_CHECK_CUDA(cudaDeviceSynchronize());
+  EVR_CHECK_CUDA(cudaMemcpy(start_end_ns, evr::g_dt_pool, 2 * static_cast<size_t>(used) * sizeof(uint64_t),
+                            cudaMemcpyDeviceToHost));
+  for (int i = 0; i < used; ++i) family[i] = evr::g_dt_family[i];
+  *count = used;
+  return 0;
+}
 int evr_profile_read(double* ms_by_family, int64_t* launches_by_family, int n) {
   EVR_REQUIRE(ms_by_family && launches_by_family && n >= evr::PF_COUNT, "evr_profile_read: need %d slots",
               (int)evr::PF_COUNT);
@@ -219,7 +257,7 @@ int evr_profile_read(double* ms_by_family, int64_t* launches_by_family, int n) {
     ms_by_family[r->family] += ms;
     launches_by_family[r->family] += 1;
   }
-  // device-timer mode: GEMM launches stamped by the kernel itself
+  // device-timer mode: launches stamped by the kernels themselves
   const int used = evr::g_dt_used.load() < evr::kProfSlots ? evr::g_dt_used.load() : evr::kProfSlots;
   if (evr::g_dt_pool != nullptr && used > 0) {
     EVR_CHECK_CUDA(cudaDeviceSynchronize());
@@ -227,8 +265,8 @@ int evr_profile_read(double* ms_by_family, int64_t* launches_by_family, int n) {
     EVR_CHECK_CUDA(cudaMemcpy(t.data(), evr::g_dt_pool, t.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
     for (int i = 0; i < used; ++i) {
       if (t[2 * i + 1] > t[2 * i]) {
-        ms_by_family[evr::PF_GEMM] += static_cast<double>(t[2 * i + 1] - t[2 * i]) * 1e-6;
-        launches_by_family[evr::PF_GEMM] += 1;
+        ms_by_family[evr::g_dt_family[i]] += static_cast<double>(t[2 * i + 1] - t[2 * i]) * 1e-6;
+        launches_by_family[evr::g_dt_family[i]] += 1;
       }
     }
   }

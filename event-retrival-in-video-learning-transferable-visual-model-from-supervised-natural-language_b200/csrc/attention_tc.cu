@@ -56,8 +56,10 @@ struct AtcArgs {
   int n_main;      // keys per S tile = round_up(min(L, 256), 16)
   int rows_alloc;  // smem rows per operand per stage = n_mtiles * 128 + 16 * lone
   int stages;
+  int pack;        // 1 when L <= 64: two (sequence, head) items share a 128-row tile, rows 0..63 | 64..127
   float c1;        // softmax scale * log2(e)
   __nv_bfloat16* out;
+  unsigned long long* prof;  // evr_profile_enable(2): device-timer slot of this launch, else nullptr
   long long* dbg;  // developer timeline (EVR_ATTN_DBG): [event][job] SM clock of CTA 0, else nullptr
 };
 
@@ -211,6 +213,29 @@ __device__ __forceinline__ void chunk_exp(const uint32_t (&v)[32], uint32_t (&pk
   }
 }
 
+// masked maximum of a 32-column chunk, four independent chains (with a constant kmax the tests fold away)
+__device__ __forceinline__ float chunk_max4(const uint32_t (&v)[32], int c, int kmax) {
+  float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+  for (int i = 0; i < 32; ++i)
+    if (c + i < kmax) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(v[i]));
+  return fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+}
+// masked exp2 of a 32-column chunk + the fp32 sum of the weights (pack mode: the thread owns its whole row, so the
+// softmax denominator needs no pass through the tensor core)
+__device__ __forceinline__ float chunk_exp_sum(const uint32_t (&v)[32], uint32_t (&pk)[16], float c1, float mc, int c,
+                                               int kmax) {
+  float s4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const float p0 = c + 2 * i < kmax ? exw(fmaf(__uint_as_float(v[2 * i]), c1, -mc)) : 0.f;
+    const float p1 = c + 2 * i + 1 < kmax ? exw(fmaf(__uint_as_float(v[2 * i + 1]), c1, -mc)) : 0.f;
+    s4[i & 3] += p0 + p1;
+    pk[i] = pack_bf16x2(p0, p1);
+  }
+  return (s4[0] + s4[1]) + (s4[2] + s4[3]);
+}
+
 // ---- warp-level MMA (m16n8k16, bf16 in, fp32 accumulate) for the lone warp: one warp, two small matrix products per
 // item, operands straight out of the 128B-swizzled tiles with ldmatrix
 __device__ __forceinline__ void mma16816(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
@@ -362,7 +387,14 @@ __device__ __forceinline__ void dbg_stamp(const AtcArgs& a, int event, int g) {
   if (a.dbg != nullptr && blockIdx.x == 0 && g < kDbgJobs) a.dbg[event * kDbgJobs + g] = clock64();
 }
 
-template <bool kCausal>
+// kPack (L <= 64, ViT-B/32's 50 tokens): a job is a PAIR of items.  Q, K and V tiles hold item 0 in rows 0..63 and item
+// 1 in rows 64..127 (two 64-row boxes of a [B][L][3 d] tensor map: rows past L arrive as zeros); S = Q K^T is the full
+// 128 x 128 product of which each row uses its own item's 64 columns; P carries zeros in the other item's columns, so
+// one P V over 128 keys serves both items.  3 072 items per ViT-B/32 layer become 1 536 tensor-core jobs whose loads
+// run four stages (192 KB) ahead -- the warp-level MMA kernel spent 2 500 warp instructions per item.
+// kPack: 0 = one item per job; 1 = pairs, sequence length read from the arguments; 50 = pairs, L = 50 folded into the
+// code (every mask of the softmax becomes a constant: the generic pack code spent a third of its instructions on them)
+template <bool kCausal, int kPack>
 __global__ void __launch_bounds__(kAtcThreads, 1)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tmap128, const __grid_constant__ CUtensorMap tmap_lone,
                     const AtcArgs a) {
@@ -375,16 +407,18 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap128, const __grid_co
   uint64_t* bars = reinterpret_cast<uint64_t*>(lone_mem + kAtcLoneBytes);
   uint64_t* full = bars;            // [4]   TMA landed
   uint64_t* empty = bars + 4;       // [4]   stage may be reloaded
-  uint64_t* s_full = bars + 8;      // [2]   S of the region is complete
-  uint64_t* p_ready = bars + 10;    // [2]   P is in TMEM
-  uint64_t* o_full = bars + 12;     // [2]   O and l of the region are complete
-  uint64_t* r_free = bars + 14;     // [2]   the region's O has been read out
-  uint64_t* col_ready = bars + 16;  // [4]   key 256's scores of the stage's item are in shared memory
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 20);
+  constexpr int kRegions = kPack != 0 ? 4 : 2;   // TMEM regions = jobs in flight (pack: 4 x 128 columns, else 2 x 256)
+  uint64_t* s_full = bars + 8;      // [kRegions]  S of the region is complete
+  uint64_t* p_ready = bars + 12;    // [kRegions]  P is in TMEM
+  uint64_t* o_full = bars + 16;     // [kRegions]  O (and l) of the region are complete
+  uint64_t* r_free = bars + 20;     // [kRegions]  the region's O has been read out
+  uint64_t* col_ready = bars + 24;  // [4]   key 256's scores of the stage's item are in shared memory
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 28);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_jobs = a.n_mtiles;
-  const int items = a.B * a.heads;
+  const int n_items = a.B * a.heads;
+  const int items = kPack != 0 ? (n_items + 1) / 2 : n_items;   // units of work the CTAs walk
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap128);
@@ -392,9 +426,11 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap128, const __grid_co
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < a.stages; ++i) {
-      mbar_init(&full[i], 1); mbar_init(&empty[i], 1 + 4 * n_jobs + 2 * a.lone); mbar_init(&col_ready[i], 1);
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], kPack != 0 ? 1 : 1 + 4 * n_jobs + 2 * a.lone);   // pack: only the P V issuer releases a stage
+      mbar_init(&col_ready[i], 1);
     }
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < kRegions; ++i) {
       mbar_init(&s_full[i], 1); mbar_init(&p_ready[i], 4); mbar_init(&o_full[i], 1); mbar_init(&r_free[i], 4);
     }
     fence_barrier_init();
@@ -408,6 +444,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap128, const __grid_co
   const uint32_t tmem_base = *tmem_slot;
   pdl_launch_dependents();
   pdl_wait();  // qkv is the previous kernel's output; `out` may still be read by the one before it
+  prof_stamp_begin(a.prof);
 
   if (warp == 0) {
     if (elect_one()) {
@@ -422,6 +459,18 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap128, const __grid_co
         dbg_stamp(a, 10, it);
         mbar_expect_tx(&full[st], tx);
         uint8_t* base = smem + st * stage_bytes;
+        if constexpr (kPack != 0) {
+#pragma unroll 1
+          for (int half = 0; half < 2; ++half) {
+            const int single = min(2 * item + half, n_items - 1);   // an odd tail repeats its item (finite data, not stored)
+            const int pb = single / a.heads, ph = single - pb * a.heads;
+#pragma unroll 1
+            for (int which = 0; which < 3; ++which)
+              tma_load_3d(base + which * op_bytes + half * (kAtcTileBytes / 2), &tmap_lone, &full[st],
+                          which * a.d + ph * 64, 0, pb, kEvictFirst);
+          }
+          continue;
+        }
         const int row0 = b * a.L;
 #pragma unroll 1
         for (int which = 0; which < 3; ++which) {
@@ -431,6 +480,49 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap128, const __grid_co
             tma_load_2d(dst + t * kAtcTileBytes, &tmap128, &full[st], col, row0 + t * 128, kEvictFirst);
           if (a.lone)
             tma_load_2d(dst + a.n_mtiles * kAtcTileBytes, &tmap_lone, &full[st], col, row0 + 256, kEvictFirst);
+        }
+      }
+    }
+  } else if (kPack != 0 && (warp == 1 || warp == 10)) {
+    // ===== pack mode: two issuers, so that neither product waits behind the other's barrier.  Warp 1: S = Q K^T of job g
+    // as soon as its stage has landed and region g % 4 has been read out; warp 10: O = P V of job g as soon as its P
+    // is in tensor memory (O lands on columns 64..127 of the region, over the half of S every row has consumed). =====
+    if (elect_one()) {
+      int g = 0;
+      if (warp == 1) {
+        const uint32_t idesc_qk = umma_idesc_f16(1, 128, 128);
+        for (int item = blockIdx.x; item < items; item += gridDim.x, ++g) {
+          const int st = g % a.stages, r = g & 3;
+          dbg_stamp(a, 11, g);
+          mbar_wait(&full[st], (g / a.stages) & 1);
+          dbg_stamp(a, 12, g);
+          mbar_wait(&r_free[r], ((g >> 2) & 1) ^ 1);
+          dbg_stamp(a, 0, g);
+          tc_fence_after();
+          const uint32_t q_addr = smem_u32(smem + st * stage_bytes);
+          const uint64_t q_desc = umma_smem_desc_sw128(q_addr), k_desc = umma_smem_desc_sw128(q_addr + op_bytes);
+#pragma unroll
+          for (int kb = 0; kb < 4; ++kb)
+            umma_f16(tmem_base + r * 128, q_desc + 2 * kb, k_desc + 2 * kb, idesc_qk, kb != 0);
+          umma_commit(&s_full[r]);
+          dbg_stamp(a, 1, g);
+        }
+      } else {
+        const uint32_t idesc_pv = umma_idesc_f16(1, 128, 64) | (1u << 16);  // B (= V) is MN-major
+        for (int item = blockIdx.x; item < items; item += gridDim.x, ++g) {
+          const int st = g % a.stages, r = g & 3;
+          mbar_wait(&full[st], (g / a.stages) & 1);   // long complete; this thread observes the TMA writes of V itself
+          mbar_wait_backoff(&p_ready[r], (g >> 2) & 1);
+          dbg_stamp(a, 2, g);
+          tc_fence_after();
+          const uint32_t region = tmem_base + r * 128;
+          const uint64_t v_desc = umma_smem_desc_sw128(smem_u32(smem + st * stage_bytes + 2 * op_bytes));
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks)
+            umma_f16_ts(region + 64, region + ks * 8, v_desc + static_cast<uint64_t>(ks) * (2048 >> 4), idesc_pv, ks != 0);
+          umma_commit(&o_full[r]);
+          umma_commit(&empty[st]);   // Q and K were consumed before P could exist: the stage is free once P V retires
+          dbg_stamp(a, 3, g);
         }
       }
     }
@@ -495,6 +587,83 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap128, const __grid_co
     // 32-column chunks without a masked key (every chunk of a causal row is masked); the rest goes 16 columns at a time
     const int nfull = kCausal ? a.n_main / 32 : key_end / 32;
     int g = 0, it = 0;
+    if constexpr (kPack != 0) {
+      // rows 0..63 belong to item 2 * pair, rows 64..127 to item 2 * pair + 1; a warp's 32 rows sit in one half.  The
+      // group walks jobs group, group + 2, ...: softmax of job g, then the read-out of its previous job g - 2, whose
+      // P V has had a whole softmax to finish.
+      const int L = kPack > 1 ? kPack : a.L;
+      const int half = quarter >> 1, r_in = row & 63;
+      const bool live = (quarter & 1) * 32 < L;      // warp-uniform
+      float inv_prev = 0.f;
+      int pair_prev = -1, g_prev = 0;
+      auto finish = [&](int gj, int pair, float inv) {
+        const int r = gj & 3;
+        if (quarter == 0 && lane == 0) dbg_stamp(a, 5, gj);
+        mbar_wait_backoff(&o_full[r], (gj >> 2) & 1);
+        if (quarter == 0 && lane == 0) dbg_stamp(a, 7, gj);
+        tc_fence_after();
+        uint32_t o[64];
+        if (live) {
+          const uint32_t region = tmem_base + r * 128 + lane_addr;
+          tmem_ld_32x32(region + 64, *reinterpret_cast<uint32_t(*)[32]>(&o[0]));
+          tmem_ld_32x32(region + 96, *reinterpret_cast<uint32_t(*)[32]>(&o[32]));
+          tmem_ld_wait();
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&r_free[r]);
+        const int single = 2 * pair + half;
+        if (live && r_in < L && single < n_items) {
+          const int ob = single / a.heads, oh = single - ob * a.heads;
+          uint4* dst = reinterpret_cast<uint4*>(a.out + (static_cast<size_t>(ob) * L + r_in) * a.d + oh * 64);
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            uint4 w;
+            w.x = pack_bf16x2(__uint_as_float(o[c * 8 + 0]) * inv, __uint_as_float(o[c * 8 + 1]) * inv);
+            w.y = pack_bf16x2(__uint_as_float(o[c * 8 + 2]) * inv, __uint_as_float(o[c * 8 + 3]) * inv);
+            w.z = pack_bf16x2(__uint_as_float(o[c * 8 + 4]) * inv, __uint_as_float(o[c * 8 + 5]) * inv);
+            w.w = pack_bf16x2(__uint_as_float(o[c * 8 + 6]) * inv, __uint_as_float(o[c * 8 + 7]) * inv);
+            dst[c] = w;
+          }
+        }
+        if (quarter == 0 && lane == 0) dbg_stamp(a, 8, gj);
+      };
+      for (int item = blockIdx.x; item < items; item += gridDim.x, ++g) {
+        if ((g & 1) != group) continue;
+        const int r = g & 3;
+        const uint32_t region = tmem_base + r * 128 + lane_addr;
+        mbar_wait_backoff(&s_full[r], (g >> 2) & 1);
+        if (quarter == 0 && lane == 0) dbg_stamp(a, 4, g);
+        tc_fence_after();
+        float inv = 0.f;
+        if (live) {
+          uint32_t va[32], vb[32], pk[16];
+          tmem_ld_32x32(region + half * 64, va);
+          tmem_ld_32x32(region + half * 64 + 32, vb);
+          tmem_ld_wait();
+          const float m = fmaxf(chunk_max4(va, 0, L), chunk_max4(vb, 32, L));
+          const float mc = m * a.c1;
+          // every score of the row is in registers: P (own 64 keys -> 32 columns) and the other item's zeros may
+          // overwrite S
+          float sum = chunk_exp_sum(va, pk, a.c1, mc, 0, L);
+          tmem_st_32x16(region + half * 32, pk);
+          sum += chunk_exp_sum(vb, pk, a.c1, mc, 32, L);
+          tmem_st_32x16(region + half * 32 + 16, pk);
+          const uint32_t zero[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+#pragma unroll
+          for (int c = 0; c < 32; c += 8) tmem_st_32x8(region + (1 - half) * 32 + c, zero);
+          tmem_st_wait();
+          inv = 1.0f / sum;
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&p_ready[r]);
+        if (quarter == 0 && lane == 0) dbg_stamp(a, 6, g);
+        if (pair_prev >= 0) finish(g_prev, pair_prev, inv_prev);
+        pair_prev = item; g_prev = g; inv_prev = inv;
+      }
+      if (pair_prev >= 0) finish(g_prev, pair_prev, inv_prev);
+    } else
     for (int item = blockIdx.x; item < items; item += gridDim.x, ++it) {
       const int b = item / a.heads, h = item - b * a.heads;
       const int st = it % a.stages;
@@ -647,6 +816,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap128, const __grid_co
 
   tc_fence_before();
   __syncthreads();
+  prof_stamp_end(a.prof);
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc<512>(tmem_base);
@@ -656,14 +826,20 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap128, const __grid_co
 bool attention_tc_supported(int L, int d, int heads) {
   return heads * 64 == d && L > 64 && L <= 257 && (d * 3) % 8 == 0;
 }
+bool attention_tc_pack_supported(int L, int d, int heads, int causal) {   // two items per tile
+  return heads * 64 == d && L >= 1 && L <= 64 && !causal && (d * 3) % 8 == 0;
+}
 
 int launch_attention_tc(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int d, int heads, int causal,
                         cudaStream_t stream) {
-  EVR_REQUIRE(attention_tc_supported(L, d, heads), "attention_tc: unsupported shape L=%d d=%d heads=%d", L, d, heads);
+  const bool pack = L <= 64;
+  EVR_REQUIRE(pack ? attention_tc_pack_supported(L, d, heads, causal) : attention_tc_supported(L, d, heads),
+              "attention_tc: unsupported shape L=%d d=%d heads=%d causal=%d", L, d, heads, causal);
   AtcArgs a{};
   a.B = B; a.L = L; a.d = d; a.heads = heads; a.causal = causal;
   a.lone = L == 257 ? 1 : 0;
-  const int main_rows = L < 256 ? L : 256;
+  a.pack = pack ? 1 : 0;
+  const int main_rows = pack ? 128 : (L < 256 ? L : 256);   // pack: 2 x 64 key slots
   a.n_mtiles = (main_rows + 127) / 128;
   a.n_main = (main_rows + 15) & ~15;
   a.rows_alloc = a.n_mtiles * 128 + kAtcLoneRows * a.lone;
@@ -685,15 +861,21 @@ int launch_attention_tc(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int
   CUtensorMap t128, t8;
   const uint64_t rows = static_cast<uint64_t>(B) * L;
   if (int r = make_tmap_2d_16b(&t128, qkv, rows, 3ull * d, 3ull * d * 2, 128, true)) return r;
-  if (int r = make_tmap_2d_16b(&t8, qkv, rows, 3ull * d, 3ull * d * 2, kAtcLoneRows, true)) return r;
+  if (pack) {   // second map: [B][L][3 d], 64-row boxes that stop at the end of their sequence
+    if (int r = make_tmap_3d_16b(&t8, qkv, B, L, 3ull * d, 3ull * d * 2, 64, true)) return r;
+  } else {
+    if (int r = make_tmap_2d_16b(&t8, qkv, rows, 3ull * d, 3ull * d * 2, kAtcLoneRows, true)) return r;
+  }
   EVR_REQUIRE(!a.lone || (stages >= 2 && !causal), "attention_tc: L = 257 needs two stages and no causal mask");
-  auto kern = causal ? attention_tc_kernel<true> : attention_tc_kernel<false>;
-  static PerDeviceMax configured[2];
-  if (configured[causal ? 1 : 0].needs(smem)) {
+  auto kern = pack ? (L == 50 ? attention_tc_kernel<false, 50> : attention_tc_kernel<false, 1>)
+                   : (causal ? attention_tc_kernel<true, 0> : attention_tc_kernel<false, 0>);
+  static PerDeviceMax configured[4];
+  if (configured[pack ? (L == 50 ? 3 : 2) : (causal ? 1 : 0)].needs(smem)) {
     EVR_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   }
-  const int items = B * heads, sms = sm_count();
+  const int items = pack ? (B * heads + 1) / 2 : B * heads, sms = sm_count();
   ProfScope ps(PF_ATTN, stream);
+  a.prof = prof_device_slot(PF_ATTN);
   EVR_CHECK_CUDA(launch_pdl(kern, dim3(items < sms ? items : sms), dim3(kAtcThreads), static_cast<size_t>(smem), stream,
                             t128, t8, a));
   EVR_CHECK_LAUNCH();
@@ -703,7 +885,7 @@ int launch_attention_tc(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int
     EVR_CHECK_CUDA(cudaMemcpy(host, a.dbg, sizeof(host), cudaMemcpyDeviceToHost));
     const long long t0 = host[0];
     const char* names[9] = {"qk_wait", "qk_issued", "p_ready_seen", "pv_issued", "s_full_seen", "pass1_done",
-                            "p_written", "o_full_seen", "o_read"};
+                            "p_written", "o_full_seen", "o_read"};   // pack mode: pass1_done = read-out begins
     for (int i = 0; i < 8; ++i)
       fprintf(stderr, "item %d: empty_wait %6lld tma_issue %6lld mma_full_wait %6lld mma_full_seen %6lld lone_start %6lld lone_end %6lld\n",
               i, host[9 * kDbgJobs + i] - t0, host[10 * kDbgJobs + i] - t0, host[11 * kDbgJobs + i] - t0,

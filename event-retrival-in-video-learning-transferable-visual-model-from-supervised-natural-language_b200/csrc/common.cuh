@@ -48,6 +48,9 @@ inline void count_launch(int n = 1) { g_launches.fetch_add(n, std::memory_order_
 int make_tmap_2d_16b(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t row_stride_bytes,
                      uint32_t box_rows, bool is_bf16);
 
+int make_tmap_3d_16b(CUtensorMap* out, const void* base, uint64_t batches, uint64_t rows, uint64_t cols,
+                     uint64_t row_stride_bytes, uint32_t box_rows, bool is_bf16);
+
 int sm_count();
 
 // cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is per device: a call site remembers the largest size it has
@@ -105,9 +108,24 @@ enum ProfFamily : int {
 extern std::atomic<int> g_profile_on;
 void prof_begin(int family, cudaStream_t s, void** token);
 void prof_end(void* token, cudaStream_t s);
-// evr_profile_enable(2): no events; the GEMM kernel stamps %globaltimer itself (GemmArgs::prof).  Returns the slot of
-// the next launch, or nullptr when that mode is off / the pool is used up.
-unsigned long long* prof_device_slot();
+// evr_profile_enable(2): no events; the GEMM, LayerNorm and attention kernels stamp %globaltimer themselves (first CTA
+// past griddepcontrol.wait, last CTA exit).  Returns the slot of the next launch, or nullptr when that mode is off /
+// the pool is used up.
+unsigned long long* prof_device_slot(int family);
+#ifdef __CUDACC__
+__device__ __forceinline__ unsigned long long prof_now_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// thread 0 of every CTA: [0] = earliest time a CTA got past griddepcontrol.wait, [1] = latest CTA exit
+__device__ __forceinline__ void prof_stamp_begin(unsigned long long* p) {
+  if (p != nullptr && threadIdx.x == 0) atomicMin(p, prof_now_ns());
+}
+__device__ __forceinline__ void prof_stamp_end(unsigned long long* p) {
+  if (p != nullptr && threadIdx.x == 0) atomicMax(p + 1, prof_now_ns());
+}
+#endif
 struct ProfScope {
   void* token = nullptr;
   cudaStream_t s;

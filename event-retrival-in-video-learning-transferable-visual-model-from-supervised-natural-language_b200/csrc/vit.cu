@@ -229,6 +229,16 @@ extern "C" int evr_vit_encode(evr_vit* h, const void* pixels, int pix_dtype, int
   return 0;
 }
 
+extern "C" int evr_layernorm(const float* in, int64_t in_stride, void* out, int64_t out_stride, int out_bf16,
+                             const float* gamma, const float* beta, int rows, int d, void* stream) {
+  EVR_REQUIRE(in && out && gamma && beta, "evr_layernorm: null pointer");
+  EVR_REQUIRE(rows >= 1 && in_stride >= d && out_stride >= d && in_stride % 4 == 0 && out_stride % 4 == 0,
+              "evr_layernorm: bad shape rows=%d d=%d strides %lld / %lld", rows, d, (long long)in_stride,
+              (long long)out_stride);
+  return launch_layernorm(in, static_cast<size_t>(in_stride), out, static_cast<size_t>(out_stride), out_bf16, gamma, beta,
+                          rows, d, static_cast<cudaStream_t>(stream));
+}
+
 extern "C" int evr_attention(const void* qkv, void* out, int B, int L, int d, int heads, int causal, int impl,
                              void* stream) {
   EVR_REQUIRE(qkv && out, "evr_attention: null pointer");

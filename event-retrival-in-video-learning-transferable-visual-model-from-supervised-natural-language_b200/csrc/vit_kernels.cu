@@ -114,9 +114,10 @@ int launch_cls_rows(float* x, const float* cls, const float* pos, int B, int L, 
 template <int D4, bool OUT_BF16>
 __global__ void __launch_bounds__(256)
 layernorm_kernel(const float* in, size_t in_stride, void* out, size_t out_stride,  // in may alias out (ln_pre)
-                 const float* __restrict__ gamma, const float* __restrict__ beta, int rows) {
+                 const float* __restrict__ gamma, const float* __restrict__ beta, int rows, unsigned long long* prof) {
   pdl_launch_dependents();
   pdl_wait();
+  prof_stamp_begin(prof);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * 8 + warp;
   if (row >= rows) return;
@@ -161,6 +162,7 @@ layernorm_kernel(const float* in, size_t in_stride, void* out, size_t out_stride
       reinterpret_cast<float4*>(static_cast<float*>(out) + static_cast<size_t>(row) * out_stride)[lane + 32 * i] = y;
     }
   }
+  prof_stamp_end(prof);
 }
 
 int launch_layernorm(const float* in, size_t in_stride, void* out, size_t out_stride, int out_bf16,
@@ -168,15 +170,16 @@ int launch_layernorm(const float* in, size_t in_stride, void* out, size_t out_st
   EVR_REQUIRE(d == 512 || d == 768 || d == 1024, "layernorm: width %d unsupported (512 | 768 | 1024)", d);
   const int blocks = (rows + 7) / 8;
   ProfScope ps(PF_LN, stream);
+  unsigned long long* prof = prof_device_slot(PF_LN);
   if (d == 512) {
-    if (out_bf16) EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<4, true>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows));
-    else EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<4, false>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows));
+    if (out_bf16) EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<4, true>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows, prof));
+    else EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<4, false>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows, prof));
   } else if (d == 768) {
-    if (out_bf16) EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<6, true>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows));
-    else EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<6, false>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows));
+    if (out_bf16) EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<6, true>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows, prof));
+    else EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<6, false>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows, prof));
   } else {
-    if (out_bf16) EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<8, true>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows));
-    else EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<8, false>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows));
+    if (out_bf16) EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<8, true>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows, prof));
+    else EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<8, false>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows, prof));
   }
   EVR_CHECK_LAUNCH();
   return 0;
@@ -235,9 +238,10 @@ __device__ __forceinline__ void ldmatrix_x4_trans(uint32_t (&r)[4], const void* 
 template <int LC>
 __global__ void __launch_bounds__(128)
 attention_short_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, int L_rt, int d, int heads,
-                       int items, float scale_log2e) {
+                       int items, float scale_log2e, unsigned long long* prof) {
   pdl_launch_dependents();
   pdl_wait();
+  prof_stamp_begin(prof);
   const int L = LC ? LC : L_rt;
   // key groups (8 keys) that hold a key / that are entirely valid: groups past nt_end cost nothing, only
   // [nt_full, nt_end) is masked.  ncu showed the loop bound by issue slots spent on ALU work, not by the tensor pipe.
@@ -381,6 +385,7 @@ attention_short_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __r
     }
     __syncthreads();  // this stage is refilled by the prefetch issued at the top of the next iteration
   }
+  prof_stamp_end(prof);
 }
 
 // One 64-key block of the flash loop for a warp's 16-query tile.  Scores stay in raw (unscaled) units: the row maximum
@@ -473,9 +478,10 @@ constexpr int kAttnLongWarps = 8;
 
 __global__ void __launch_bounds__(kAttnLongWarps * 32, 2)
 attention_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, int L, int d,
-                 float scale_log2e, int causal) {
+                 float scale_log2e, int causal, unsigned long long* prof) {
   pdl_launch_dependents();
   pdl_wait();
+  prof_stamp_begin(prof);
   extern __shared__ __align__(16) uint8_t attn_smem[];
   const int h = blockIdx.x, b = blockIdx.y;
   const int Lp = (L + 63) & ~63;
@@ -622,6 +628,7 @@ attention_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restric
       *reinterpret_cast<uint32_t*>(out + (row0 + r) * d + h * 64 + 2 * lane) = pack2_bf16(tx * inv, ty * inv);
     }
   }
+  prof_stamp_end(prof);
 }
 
 static bool attention_tc_enabled() {
@@ -641,7 +648,8 @@ int launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L,
 int launch_attention_impl(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int d, int heads, int causal,
                           int impl, cudaStream_t stream) {
   EVR_REQUIRE(heads * 64 == d, "attention: head dim must be 64 (d=%d heads=%d)", d, heads);
-  if (impl == 2 || (impl == 0 && attention_tc_enabled() && attention_tc_supported(L, d, heads)))
+  if (impl == 2 || (impl == 0 && attention_tc_enabled() &&
+                    (attention_tc_supported(L, d, heads) || attention_tc_pack_supported(L, d, heads, causal))))
     return launch_attention_tc(qkv, out, B, L, d, heads, causal, stream);
   if (L <= 64 && !causal) {
     static PerDeviceMax configured_short;
@@ -659,7 +667,7 @@ int launch_attention_impl(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, i
     ProfScope ps(PF_ATTN, stream);
     EVR_CHECK_CUDA(launch_pdl(L == 50 ? attention_short_kernel<50> : attention_short_kernel<0>, dim3(grid), dim3(128),
                               2 * kAttnStageBytes, stream, qkv, out, L, d, heads, items,
-                              0.125f * 1.4426950408889634f));
+                              0.125f * 1.4426950408889634f, prof_device_slot(PF_ATTN)));
     EVR_CHECK_LAUNCH();
     return 0;
   }
@@ -673,7 +681,7 @@ int launch_attention_impl(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, i
   }
   ProfScope ps(PF_ATTN, stream);
   EVR_CHECK_CUDA(launch_pdl(attention_kernel, dim3(heads, B), dim3(kAttnLongWarps * 32), smem, stream, qkv, out, L, d,
-                            0.125f * 1.4426950408889634f, causal));
+                            0.125f * 1.4426950408889634f, causal, prof_device_slot(PF_ATTN)));
   EVR_CHECK_LAUNCH();
   return 0;
 }

@@ -25,6 +25,7 @@ int launch_attention(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L,
                      cudaStream_t stream);
 // the same on tcgen05 / TMEM (attention_tc.cu), 64 < L <= 257; launch_attention dispatches to it
 bool attention_tc_supported(int L, int d, int heads);
+bool attention_tc_pack_supported(int L, int d, int heads, int causal);  // L <= 64: two items per 128-row tile
 int launch_attention_tc(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int L, int d, int heads, int causal,
                         cudaStream_t stream);
 // impl 0: dispatch (tcgen05 where supported), 1: warp-level MMA kernels, 2: tcgen05 or an error

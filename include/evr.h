@@ -25,10 +25,13 @@ int64_t evr_launch_count(void);
  * Families: 0 tcgen05 GEMM, 1 attention core, 2 LayerNorm, 3 other ViT kernels, 4 fused scan+top-k,
  * 5 final select/merge, 6 store prepare / re-score.  n >= 7.
  * evr_profile_enable(2): no events (an event between two kernels costs ~5 us and breaks their programmatic overlap);
- * instead every GEMM launch records, on the device, the earliest %globaltimer at which one of its CTAs got past
- * griddepcontrol.wait and the latest CTA exit; evr_profile_read then reports family 0 from those stamps. */
+ * instead every GEMM, LayerNorm and attention launch records, on the device, the earliest %globaltimer at which one of
+ * its CTAs got past griddepcontrol.wait and the latest CTA exit; evr_profile_read then reports families 0-2 from those
+ * stamps, and evr_profile_timeline hands back the raw (start, end) pairs in launch order (start_end_ns[2 i], [2 i + 1],
+ * family[i]; *count launches, at most `capacity`) so that the idle time between kernels can be measured too. */
 int evr_profile_enable(int on);
 int evr_profile_read(double* ms_by_family, int64_t* launches_by_family, int n);
+int evr_profile_timeline(uint64_t* start_end_ns, int* family, int capacity, int* count);
 
 /* ---- store preparation -------------------------------------------------------------
  * replaces  embeddings / np.linalg.norm(embeddings, axis=-1, keepdims=True)
@@ -177,6 +180,13 @@ int evr_jpeg_backend(const evr_jpeg* h); /* nvjpegBackend_t in use: 3 = hardware
 int evr_jpeg_info(evr_jpeg* h, const uint8_t* data, size_t length, int* width, int* height, int* components);
 int evr_jpeg_decode_batch(evr_jpeg* h, const uint8_t* const* data, const size_t* lengths, int n, int H, int W,
                           uint8_t* dst, void* stream);
+
+/* Building block exported for the parity tests: LayerNorm of the residual stream as the towers run it
+ * (openai/CLIP clip/model.py `LayerNorm`: fp32 statistics, eps 1e-5): out[r, :] = (in[r, :] - mean) * rstd * gamma + beta
+ * for `rows` rows of width d (512 | 768 | 1024), strides in elements, output bf16 (out_bf16 = 1) or fp32 (may be in
+ * place).  One row per warp; 59 MB per launch at 12 800 x 768 runs at 5.4 TB/s whether the rows come from HBM or L2. */
+int evr_layernorm(const float* in, int64_t in_stride, void* out, int64_t out_stride, int out_bf16, const float* gamma,
+                  const float* beta, int rows, int d, void* stream);
 
 /* building-block attention core exported for the parity tests: softmax(q k^T / 8 [+ causal mask]) v per
  * (sequence, head), head dim 64.  qkv bf16 [B L, 3 d] (q | k | v as the in_proj GEMM writes it), out bf16 [B L, d].

@@ -11,7 +11,7 @@ import __graft_entry__ as ge  # noqa: E402
 pkg = ge.load_package()
 lib, check, ptr, stream = pkg._lib.lib, pkg._lib.check, pkg._lib.ptr, pkg._lib.current_stream_ptr
 dev = torch.device("cuda:0")
-for name, B, L, d, heads, causal in (("ViT-L/14", 128, 257, 1024, 16, 0), ("ViT-B/16", 256, 197, 768, 12, 0),
+for name, B, L, d, heads, causal in (("ViT-B/32", 256, 50, 768, 12, 0), ("ViT-L/14", 128, 257, 1024, 16, 0), ("ViT-B/16", 256, 197, 768, 12, 0),
                                      ("text", 64, 77, 512, 8, 1), ("text-1", 1, 77, 512, 8, 1)):
     bufs = [torch.randn((B * L, 3 * d), device=dev).to(torch.bfloat16) for _ in range(3)]   # rotate: inputs not in L2
     out = torch.empty((B * L, d), dtype=torch.bfloat16, device=dev)

@@ -39,6 +39,13 @@ CASES = [  # B, L, d, heads, causal
     (2, 77, 768, 12, True),        # ViT-L/14's text tower
     (2, 65, 768, 12, False), (2, 128, 768, 12, False), (1, 256, 768, 12, False), (2, 129, 768, 12, True),
     (40, 257, 1024, 16, False),    # 640 items: several per CTA, stage and region barriers wrap many times
+    # L <= 64: two (image, head) items share one 128-row tile (rows past L arrive as zeros, P is block-diagonal)
+    (3, 50, 768, 12, False),       # ViT-B/32
+    (64, 50, 768, 12, False),      # 384 pairs: several per CTA
+    (7, 33, 192, 3, False),        # 21 items: the last pair holds one item
+    (1, 64, 64, 1, False),         # a single item, every key slot used
+    (5, 17, 512, 8, False),        # the second warp of each half has no live row
+    (2, 1, 128, 2, False),         # one token: softmax over one key
 ]
 
 
@@ -61,14 +68,16 @@ def test_attention_matches_fp32_reference(pkg, cuda, B, L, d, heads, causal, imp
 
 
 def test_tcgen05_kernel_is_what_the_towers_run(pkg, cuda):
-    """impl 0 dispatches 64 < L <= 257 to the tcgen05 kernel: bit-identical outputs; L = 50 stays on the short kernel."""
+    """impl 0 dispatches every non-causal L <= 257 (and causal 64 < L <= 257) to the tcgen05 kernel: bit-identical
+    outputs; a causal short sequence stays on the warp-level kernel and impl 2 refuses it."""
     g = torch.Generator(device=cuda).manual_seed(3)
     qkv = torch.randn((2 * 257, 3 * 1024), generator=g, device=cuda).to(torch.bfloat16)
     assert torch.equal(_run(pkg, qkv, 2, 257, 1024, 16, False, 0), _run(pkg, qkv, 2, 257, 1024, 16, False, 2))
     qkv = torch.randn((3 * 50, 3 * 768), generator=g, device=cuda).to(torch.bfloat16)
-    assert torch.equal(_run(pkg, qkv, 3, 50, 768, 12, False, 0), _run(pkg, qkv, 3, 50, 768, 12, False, 1))
+    assert torch.equal(_run(pkg, qkv, 3, 50, 768, 12, False, 0), _run(pkg, qkv, 3, 50, 768, 12, False, 2))
+    assert torch.equal(_run(pkg, qkv, 3, 50, 768, 12, True, 0), _run(pkg, qkv, 3, 50, 768, 12, True, 1))
     with pytest.raises(pkg._lib.EvrError, match="unsupported shape"):
-        _run(pkg, qkv, 3, 50, 768, 12, False, 2)
+        _run(pkg, qkv, 3, 50, 768, 12, True, 2)
 
 
 def test_rows_of_other_sequences_do_not_leak(pkg, cuda):
@@ -76,6 +85,15 @@ def test_rows_of_other_sequences_do_not_leak(pkg, cuda):
     lies past the end of the buffer): changing those rows must not change this image's output."""
     g = torch.Generator(device=cuda).manual_seed(9)
     B, L, d, heads = 3, 197, 768, 12
+    qkv = torch.randn((B * L, 3 * d), generator=g, device=cuda).to(torch.bfloat16)
+    base = _run(pkg, qkv, B, L, d, heads, False, 2)
+    other = qkv.clone()
+    other[L:2 * L] = torch.randn((L, 3 * d), generator=g, device=cuda).to(torch.bfloat16) * 30
+    moved = _run(pkg, other, B, L, d, heads, False, 2)
+    assert torch.equal(moved[:L], base[:L]) and torch.equal(moved[2 * L:], base[2 * L:])
+    assert not torch.equal(moved[L:2 * L], base[L:2 * L])
+    # packed pairs (L = 50): image 1 shares tiles with neither neighbour's values
+    L = 50
     qkv = torch.randn((B * L, 3 * d), generator=g, device=cuda).to(torch.bfloat16)
     base = _run(pkg, qkv, B, L, d, heads, False, 2)
     other = qkv.clone()

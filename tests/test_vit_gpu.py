@@ -212,8 +212,9 @@ def test_small_batch_graph_replay_is_identical(pkg, cuda, b32):
 
 
 def test_profile_modes_do_not_change_results(pkg, cuda, b32):
-    """evr_profile_enable(1) brackets launches with events, (2) lets the GEMM kernel stamp %globaltimer: same outputs,
-    the same number of GEMM launches reported by both, positive times."""
+    """evr_profile_enable(1) brackets launches with events, (2) lets the GEMM / LayerNorm / attention kernels stamp
+    %globaltimer: same outputs, the same number of launches reported by both, positive times, and a timeline whose
+    kernels do not overlap (every stamp is taken after griddepcontrol.wait)."""
     visual, u8, pix, ref = b32
     enc = pkg.vit.VisionEncoder.from_state_dict(visual.state_dict(), "ViT-B/32", device=cuda, max_batch=64)
     x = pix[:40].to(cuda)  # above the captured-graph batch limit: plain launches in every mode
@@ -224,12 +225,18 @@ def test_profile_modes_do_not_change_results(pkg, cuda, b32):
         out = enc.encode(x).clone()
         torch.cuda.synchronize()
         fam = pkg._lib.profile_read()
+        timeline = pkg._lib.profile_timeline() if mode == 2 else None
         pkg._lib.profile_enable(False)
         assert torch.equal(out, base)
         ms, n = fam["gemm_tc"]
         assert n == 2 + 4 * 12 and ms > 0.0, (mode, fam)  # patch + projection + 4 per block
         counts[mode] = fam
-    assert counts[2]["layernorm"][1] == 0 and counts[1]["layernorm"][1] == 2 + 2 * 12  # events only in mode 1
+    for f, n in (("layernorm", 2 + 2 * 12), ("attention", 12)):
+        assert counts[1][f][1] == n and counts[2][f][1] == n and counts[2][f][0] > 0.0, (f, counts)
+    assert counts[2]["vit_misc"][1] == 0                     # the small kernels carry no device stamp
+    assert len(timeline) == 2 + 4 * 12 + 2 + 2 * 12 + 12
+    ordered = sorted(timeline, key=lambda t: t[1])
+    assert all(a[2] <= b[1] for a, b in zip(ordered, ordered[1:]))   # one kernel of the chain at a time
 
 
 def test_gemm_bits_do_not_depend_on_tile_width(pkg, cuda, monkeypatch):
