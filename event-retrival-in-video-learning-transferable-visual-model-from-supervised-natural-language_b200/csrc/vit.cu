@@ -2,6 +2,7 @@
 // sequence of encode_image.  Replaces model.encode_image(batch) of openai/CLIP (call sites
 // Backend/embedding.py:49, Backend/services/embedding_service.py:41,414,490); structure per
 // clip/model.py VisionTransformer.forward.
+#include <cstdlib>
 #include <vector>
 
 #include "../../include/evr.h"
@@ -140,7 +141,11 @@ extern "C" int evr_vit_create(const evr_vit_cfg* cfg, const void* const* w, int 
     cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, dev);
     cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, dev);
     size_t want = rows * d * 4;
-    if (want > static_cast<size_t>(max_persist)) want = max_persist;
+    if (want > static_cast<size_t>(max_persist)) want = 0;   // does not fit: no carve-out at all (see encode_chunk)
+    if (const char* e = getenv("EVR_L2_PERSIST_MB")) {   // experiments: cap (0 = no window at all)
+      const size_t cap = static_cast<size_t>(atoi(e) > 0 ? atoi(e) : 0) << 20;
+      if (want > cap) want = cap;
+    }
     if (want > 0 && max_window > 0 && cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want) == cudaSuccess) {
       h->l2_persist = want;
       h->l2_window_max = max_window;
@@ -201,7 +206,12 @@ static int encode_chunk(evr_vit* h, const void* pixels, int pix_dtype, int B, vo
   const int M = B * L;
   // K1: im2col reads the caller's pixels; everything up to the projection lives in handle buffers (graph-able)
   if (launch_im2col(pixels, pix_dtype, B, h->cfg.image_size, h->cfg.patch, h->K0p, h->a0, s)) return 1;
-  const bool window = B > GraphCache::kMaxBatch;  // small batches: x is a few MB, no window (and none in the graph)
+  // small batches: x is a few MB, no window (and none in the graph).  A stream that does not fit the persisting
+  // carve-out gets none either: a partial window (hitRatio < 1) takes that much of L2 away from the bf16 activations
+  // and the weights for a fraction of x -- device-stamped A/B (scripts/gap_probe.py): ViT-B/16 at B = 256 (155 MB)
+  // 14.5 -> 11.1 ms per batch without it, ViT-L/14 at B = 128 (135 MB) 23.1 -> 21.7 ms; ViT-B/32 (39 MB, fits)
+  // 2.79 -> 2.76 ms with it.
+  const bool window = B > GraphCache::kMaxBatch && static_cast<size_t>(M) * d * sizeof(float) <= h->l2_persist;
   if (window) set_residual_window(h, static_cast<size_t>(M) * d * sizeof(float), s);
   const int r = run_chain(h->graphs, B, s, [&](cudaStream_t cs) { return encode_body(h, B, cs); });
   if (r) return r;
