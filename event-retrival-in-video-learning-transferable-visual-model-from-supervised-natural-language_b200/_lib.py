@@ -43,6 +43,8 @@ SIGNATURES = {
     "evr_topk_workspace_bytes": (c_int, [c_int64, c_int, c_int, c_int, ctypes.POINTER(c_size_t)]),
     "evr_topk_search": (c_int, [c_void_p, c_int64, c_int, c_int64, c_void_p, c_int, c_int, c_void_p, c_void_p,
                                 c_void_p, c_size_t, c_void_p]),
+    "evr_topk_search_static": (c_int, [c_void_p, c_int64, c_int, c_int64, c_void_p, c_int, c_int, c_void_p, c_void_p,
+                                       c_void_p]),
     "evr_topk_merge": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "evr_topk_large_workspace_bytes": (c_int, [c_int64, c_int, c_int64, ctypes.POINTER(c_size_t)]),
     "evr_topk_search_large": (c_int, [c_void_p, c_int64, c_int, c_int64, c_void_p, c_int, c_int64, c_void_p, c_void_p,

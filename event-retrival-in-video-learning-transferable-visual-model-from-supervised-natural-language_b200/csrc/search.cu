@@ -23,6 +23,7 @@
 
 #include <atomic>
 #include <cstdlib>
+#include <mutex>
 
 #include "../../include/evr.h"
 #include "common.cuh"
@@ -1111,6 +1112,52 @@ extern "C" int evr_topk_search(const void* store, int64_t N, int D, int64_t row_
   }
   EVR_CHECK_LAUNCH();
   return 0;
+}
+
+// ---- the scan with its scratch in a static device array -------------------------------------------------------------
+// No counterpart in the reference; added for callers that cannot allocate
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The array belongs to this
+// module: every GPU that loads the library holds its EVR_TOPK_STATIC_SCRATCH_BYTES until the process exits.  In host code
+// `g_static_scan_scratch` is only a stand-in for the symbol -- the device address comes from cudaGetSymbolAddress, once
+// per device with that device current.
+static __device__ __align__(256) unsigned char g_static_scan_scratch[EVR_TOPK_STATIC_SCRATCH_BYTES];
+
+static int static_scan_scratch(void** out) {
+  static std::mutex mu;
+  static void* address[64] = {};
+  int dev = 0;
+  EVR_CHECK_CUDA(cudaGetDevice(&dev));
+  EVR_REQUIRE(dev >= 0 && dev < 64, "evr_topk_search_static: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (address[dev] == nullptr) {
+    void* p = nullptr;
+    EVR_CHECK_CUDA(cudaGetSymbolAddress(&p, g_static_scan_scratch));
+    EVR_REQUIRE(p != nullptr && (reinterpret_cast<uintptr_t>(p) & 255) == 0,
+                "evr_topk_search_static: bad address %p for the static scratch array", p);
+    address[dev] = p;
+  }
+  *out = address[dev];
+  return 0;
+}
+
+extern "C" int evr_topk_search_static(const void* store, int64_t N, int D, int64_t row_offset, const void* queries,
+                                      int Q, int k, float* out_scores, int64_t* out_idx, void* stream) {
+  EVR_REQUIRE(store && queries && out_scores && out_idx, "evr_topk_search_static: null pointer");
+  ScanPlan p;
+  if (int r = plan_scan(N, D, Q, k, &p)) return r;
+  EVR_REQUIRE(p.total_bytes <= static_cast<size_t>(EVR_TOPK_STATIC_SCRATCH_BYTES),
+              "evr_topk_search_static: N=%lld D=%d Q=%d k=%d needs %zu bytes of scratch, the static array holds %zu "
+              "(use evr_topk_search with a caller-owned workspace)", (long long)N, D, Q, k, p.total_bytes,
+              static_cast<size_t>(EVR_TOPK_STATIC_SCRATCH_BYTES));
+  void* ws = nullptr;
+  if (int r = static_scan_scratch(&ws)) return r;
+  // The array keeps the previous call's contents.  The candidate lists need no clearing (a list is written before it is
+  // read); the counters, thresholds and slice flags behind them start every call from zero.
+  const size_t tail = p.total_bytes > p.lists_bytes ? p.total_bytes - p.lists_bytes : 0;
+  if (tail) EVR_CHECK_CUDA(cudaMemsetAsync(static_cast<uint8_t*>(ws) + p.lists_bytes, 0, tail,
+                                           static_cast<cudaStream_t>(stream)));
+  return evr_topk_search(store, N, D, row_offset, queries, Q, k, out_scores, out_idx, ws,
+                         static_cast<size_t>(EVR_TOPK_STATIC_SCRATCH_BYTES), stream);
 }
 
 extern "C" int evr_topk_merge(const float* scores, const int64_t* idx, int P, int Q, int k, float* out_scores,
