@@ -112,7 +112,36 @@ struct ScanArgs {
   int stages;          // depth of the store-row smem ring actually used (<= kScanStages; 2 at D = 768)
   int row_evict_last;  // A/B knob (EVR_SCAN_EVICT_LAST=1): store rows stay in L2 as long as possible
   int tile_stride;     // sample pass: tile t of the launch reads store tile t * tile_stride (1 in the full scan)
+  int qt_group;        // query tiles that walk the store together (a pass); num_qt = one pass (items slice-major)
+  int rotate;          // 1: the query tiles of a pass start a slice at different tiles (and wrap around)
 };
+
+// item -> (query tile, slice).  The query tiles are taken `qt_group` at a time; inside such a pass items are
+// slice-major, so the tiles of a pass read a slice together and the passes walk the store one after the other.
+struct ScanItem { int qt, slice, lane_in_group, group_size; };
+__device__ __forceinline__ ScanItem scan_item(const ScanArgs& a, int item) {
+  ScanItem r;
+  const int G = a.qt_group;
+  const int per_pass = G * a.num_slices;
+  int pass = item / per_pass;
+  const int last = (a.num_qt - 1) / G;
+  if (pass > last) pass = last;
+  const int rem = item - pass * per_pass;
+  r.group_size = min(G, a.num_qt - pass * G);
+  r.slice = rem / r.group_size;
+  r.lane_in_group = rem - r.slice * r.group_size;
+  r.qt = pass * G + r.lane_in_group;
+  return r;
+}
+// tile visited at step i of an item's walk over [t0, t1)
+__device__ __forceinline__ int64_t scan_tile(const ScanArgs& a, const ScanItem& it, int64_t t0, int64_t t1, int64_t i) {
+  if (!a.rotate) return t0 + i;
+  const int64_t n = t1 - t0;
+  const int64_t rot = (static_cast<int64_t>(it.lane_in_group) * n) / it.group_size;
+  int64_t j = i + rot;
+  if (j >= n) j -= n;
+  return t0 + j;
+}
 
 // Warp-cooperative exact prune of one query's candidate list to its top-k.  All 32 lanes call with the
 // same arguments.  Returns the key of the k-th best entry (new admission threshold).
@@ -224,7 +253,8 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       uint64_t row_policy = args.num_qt > 1 ? kEvictNormal : kEvictFirst;
       if (args.row_evict_last) row_policy = kEvictLast;
       for (int item = unit; item < num_items; item += num_units) {
-        const int qt = item % args.num_qt, slice = item / args.num_qt;
+        const ScanItem si = scan_item(args, item);
+        const int qt = si.qt, slice = si.slice;
         mbar_wait(q_empty, qphase ^ 1);  // MMAs of the previous item no longer read the query tile
         const int q_row = (qt * CG + static_cast<int>(rank)) * kScanQTile;
         if constexpr (CG == 2) {
@@ -241,7 +271,8 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         const int64_t t0 = static_cast<int64_t>(slice) * args.tiles_per_slice;
         int64_t t1 = t0 + args.tiles_per_slice;
         if (t1 > total_tiles) t1 = total_tiles;
-        for (int64_t t = t0; t < t1; ++t) {
+        for (int64_t ti = 0; ti < t1 - t0; ++ti) {
+          const int64_t t = scan_tile(args, si, t0, t1, ti);
           const int row = static_cast<int>(t * args.tile_stride * kRowTile) +
                           static_cast<int>(rank) * kScanRowTile;  // this CTA's half of the (strided) tile
           for (int kb = 0; kb < num_kb; ++kb) {
@@ -267,7 +298,7 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       uint32_t phase = 0, aphase = 0, qphase = 0;
       const uint32_t q_addr = smem_u32(smem_q);
       for (int item = unit; item < num_items; item += num_units) {
-        const int slice = item / args.num_qt;
+        const int slice = scan_item(args, item).slice;
         mbar_wait(q_full, qphase);
         qphase ^= 1;
         tc_fence_after();
@@ -308,7 +339,8 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     int as = 0;
     uint32_t aphase = 0;
     for (int item = unit; item < num_items; item += num_units) {
-      const int qt = item % args.num_qt, slice = item / args.num_qt;
+      const ScanItem si = scan_item(args, item);
+      const int qt = si.qt, slice = si.slice;
       const int q0 = (qt * CG + static_cast<int>(rank)) * kScanQTile + quad * 32;  // first query of this warp
       const bool q_valid = q0 + lane < args.Q;
       // the candidate list of (slice, query) is filled in place; the final select kernel reads it with its count
@@ -339,7 +371,8 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       const int64_t t0 = static_cast<int64_t>(slice) * args.tiles_per_slice;
       int64_t t1 = t0 + args.tiles_per_slice;
       if (t1 > total_tiles) t1 = total_tiles;
-      for (int64_t t = t0; t < t1; ++t) {
+      for (int64_t ti = 0; ti < t1 - t0; ++ti) {
+        const int64_t t = scan_tile(args, si, t0, t1, ti);
         mbar_wait(&acc_full[as], aphase);
         tc_fence_after();
         const int row_base = static_cast<int>(t * kRowTile);
@@ -831,6 +864,7 @@ rescore_kernel(const __half* __restrict__ store, int64_t N, int D, const __half*
 struct ScanCore {  // one launch of topk_scan_kernel over N rows
   int cg;  // 1: one CTA per unit, 2: CTA pairs (cta_group::2)
   int epl, cap, num_qt, q_pad, num_slices, tiles_per_slice, grid, ring;
+  int qt_group, rotate;  // see ScanArgs
 };
 struct ScanPlan {
   ScanCore main, pre;
@@ -852,6 +886,15 @@ static void plan_core(int64_t N, int D, int Q, int k, int sm_total, ScanCore* p)
   p->cap = 32 * p->epl;
   p->num_qt = (Q + qtile - 1) / qtile;
   p->q_pad = p->num_qt * qtile;
+  p->qt_group = p->num_qt;
+  // the query tiles that share a slice start it at different tiles (and wrap around): a row tile is then fetched by one
+  // unit and found in L2 by the others over the length of an item, instead of being requested by all of them at once
+  // (config 3, ncu: DRAM reads 106 -> 73 GB; 1-3 % less time at 20-40 query tiles, neutral below 4)
+  p->rotate = p->num_qt >= 4 ? 1 : 0;
+  if (const char* e = getenv("EVR_SCAN_QT_GROUP")) {   // experiment: passes of g query tiles (measured: 2.5 x MORE DRAM reads)
+    if (atoi(e) > 0 && atoi(e) < p->num_qt) p->qt_group = atoi(e);
+  }
+  if (const char* e = getenv("EVR_SCAN_ROTATE")) p->rotate = e[0] == '1' ? 1 : 0;
   const int64_t tiles = (N + rowtile - 1) / rowtile;
   int S;
   if (p->num_qt == 1) {
@@ -885,7 +928,7 @@ static void plan_core(int64_t N, int D, int Q, int k, int sm_total, ScanCore* p)
     // (profiles/r02_scan_c3_traffic.txt): 73-82 GB and 10 % less time; the hit rate stays near 72 % whatever the slice
     // size (6-48 MB in flight) and whether or not the units are skewed against each other inside a slice, i.e. what is
     // left is not a capacity effect (the missing step is a TMA-multicast cluster sharing each row tile).
-    const int conc = (sms + p->num_qt - 1) / p->num_qt;
+    const int conc = (sms + p->qt_group - 1) / p->qt_group;
     int64_t inflight_mb = 12;
     if (const char* e = getenv("EVR_SCAN_INFLIGHT_MB")) {   // tuning knob
       if (atoi(e) > 0) inflight_mb = atoi(e);
@@ -902,8 +945,13 @@ static void plan_core(int64_t N, int D, int Q, int k, int sm_total, ScanCore* p)
   p->num_slices = static_cast<int>((tiles + p->tiles_per_slice - 1) / p->tiles_per_slice);
   // candidate lists: one per slice while there are few; otherwise a ring that slice s shares with s - ring, s - 2 ring,
   // ... (the kernel orders them with a flag per (32 queries, slice)); deep enough for the slices in flight plus drift
-  const int conc = p->num_qt > 1 ? (sms + p->num_qt - 1) / p->num_qt : p->num_slices;
-  int ring = 2 * conc + 6;
+  const int conc = p->num_qt > 1 ? (sms + p->qt_group - 1) / p->qt_group : p->num_slices;
+  // (2 conc + 6 was too shallow: at config 3, conc = 2, the epilogue warps stood at the flag of slice - 10 often enough
+  // to cost 8 % -- scripts/scan_plan_probe.py: 89.8 ms at ring 10, 82-84 ms at 16-40)
+  int ring = 2 * conc + 16;
+  if (const char* e = getenv("EVR_SCAN_RING")) {   // experiments: how far the units may drift apart, in slices
+    if (atoi(e) > 0) ring = atoi(e);
+  }
   if (p->num_qt == 1 || ring > p->num_slices) ring = p->num_slices;
   p->ring = ring;
   const long long items = static_cast<long long>(p->num_qt) * p->num_slices;
@@ -1037,6 +1085,8 @@ static int run_scan(const ScanCore& c, const void* store, int64_t N, int64_t N_s
   a.init_thresh = init_thresh;
   a.lists = lists; a.counts = counts; a.group_max = group_max; a.groups = groups;
   a.ring = c.ring; a.list_thresh = list_thresh; a.done = done; a.epoch = epoch;
+  a.qt_group = c.qt_group > 0 ? c.qt_group : c.num_qt;
+  a.rotate = c.rotate;
   CUtensorMap tq, ts;
   if (int r = make_tmap_2d_16b(&tq, queries, Q, D, static_cast<uint64_t>(D) * 2, kScanQTile, false)) return r;
   if (int r = make_tmap_2d_16b(&ts, store, N_store, D, static_cast<uint64_t>(D) * 2, kScanRowTile, false)) return r;

@@ -42,7 +42,12 @@ elif case in ("encode1", "text1"):
     torch.cuda.synchronize()
     print(case, "ok", float(out.float().abs().sum()))
 else:
-    n, q = {"scan_c3": (10_000_000, 10_000), "scan_big": (2_000_000, 10_000), "scan_small": (10_000_000, 32), "scan_q1": (10_000_000, 1),
+    if case.startswith("scan:"):      # scan:<rows>:<queries>
+        _, n_s, q_s = case.split(":")
+        custom = (int(n_s), int(q_s))
+    else:
+        custom = None
+    n, q = custom or {"scan_c3": (10_000_000, 10_000), "scan_big": (2_000_000, 10_000), "scan_small": (10_000_000, 32), "scan_q1": (10_000_000, 1),
             "scan_q128": (10_000_000, 128)}[case]
     store = pkg.search.FrameStore(bench.make_store(torch, dev, n, seed=2))
     g = torch.Generator().manual_seed(3)
