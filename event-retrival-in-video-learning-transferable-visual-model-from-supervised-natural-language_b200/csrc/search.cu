@@ -947,8 +947,10 @@ static void plan_core(int64_t N, int D, int Q, int k, int sm_total, ScanCore* p)
   // ... (the kernel orders them with a flag per (32 queries, slice)); deep enough for the slices in flight plus drift
   const int conc = p->num_qt > 1 ? (sms + p->qt_group - 1) / p->qt_group : p->num_slices;
   // (2 conc + 6 was too shallow: at config 3, conc = 2, the epilogue warps stood at the flag of slice - 10 often enough
-  // to cost 8 % -- scripts/scan_plan_probe.py: 89.8 ms at ring 10, 82-84 ms at 16-40)
-  int ring = 2 * conc + 16;
+  // to cost 8 % -- scripts/scan_plan_probe.py: 89.8 ms at ring 10, 82-84 ms at 16-40 -- and, by holding units back at
+  // different moments, to pull the units that share a slice apart: DRAM reads 80-113 GB at ring 10, 21-29 GB at 20,
+  // 15-20 GB at 32, 14.5 GB at 48 for the 10.24 GB store; 32 lists of 4 KB per query = 1.3 GB of workspace at Q = 10 000)
+  int ring = 2 * conc + 28;
   if (const char* e = getenv("EVR_SCAN_RING")) {   // experiments: how far the units may drift apart, in slices
     if (atoi(e) > 0) ring = atoi(e);
   }

@@ -62,8 +62,8 @@ int evr_topk_search(const void* store, int64_t N, int D, int64_t row_offset, con
  * reference: added for callers that cannot allocate (code under CUDA graph
  * capture, tight serving loops, harnesses that forbid cudaMalloc).  The call allocates nothing -- no cudaMalloc /
  * cudaFree, no allocating library routine; inputs and outputs are the caller's.  Limit: the request must fit
- * EVR_TOPK_STATIC_SCRATCH_BYTES (80 MiB: every query batch Q <= 256 with k <= 128 at any N; e.g. Q = 1024 or k = 1024 do
- * not), otherwise the call fails with a message naming both sizes and evr_topk_search is the entry point to use.  Every
+ * EVR_TOPK_STATIC_SCRATCH_BYTES (80 MiB: every query batch Q <= 128 with k <= 128, and Q <= 256 with k <= 100, at any N; e.g.
+ * Q = 1024 or k = 1024 do not), otherwise the call fails with a message naming both sizes and evr_topk_search is the entry point to use.  Every
  * GPU that loads the library holds the array until the process exits.  All calls on a device share it: calls that
  * overlap on the GPU (two streams, two threads) race -- serialise them; results are bit-identical to evr_topk_search. */
 #define EVR_TOPK_STATIC_SCRATCH_BYTES (80u << 20)
