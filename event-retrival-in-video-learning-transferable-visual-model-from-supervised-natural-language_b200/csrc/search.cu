@@ -951,6 +951,12 @@ static void plan_core(int64_t N, int D, int Q, int k, int sm_total, ScanCore* p)
   // different moments, to pull the units that share a slice apart: DRAM reads 80-113 GB at ring 10, 21-29 GB at 20,
   // 15-20 GB at 32, 14.5 GB at 48 for the 10.24 GB store; 32 lists of 4 KB per query = 1.3 GB of workspace at Q = 10 000)
   int ring = 2 * conc + 28;
+  // The units' positions are a random walk, so a longer scan needs a deeper ring to stay clear of the flags: 50 M rows,
+  // Q = 10 000: 447 ms at ring 32, 422 at 64, 391 at 96 (= the per-row time of the 10 M scan), 395 at 128.
+  if (N > 10000000) {
+    const int64_t over = N - 10000000 < 40000000 ? N - 10000000 : 40000000;
+    ring += static_cast<int>(64 * over / 40000000);
+  }
   if (const char* e = getenv("EVR_SCAN_RING")) {   // experiments: how far the units may drift apart, in slices
     if (atoi(e) > 0) ring = atoi(e);
   }

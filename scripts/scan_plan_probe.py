@@ -30,14 +30,15 @@ def one(q=10_000, n=10_000_000, iters=8):
         torch.cuda.synchronize()
         times.append(e0.elapsed_time(e1))
     times.sort()
-    print(json.dumps({"env": os.environ.get("EVR_PROBE_LABEL", ""), "Q": q, "median_ms": round(times[len(times) // 2], 3),
+    print(json.dumps({"env": os.environ.get("EVR_PROBE_LABEL", ""), "Q": q, "N": n, "median_ms": round(times[len(times) // 2], 3),
                       "min_ms": round(times[0], 3), "qps": round(q / times[len(times) // 2] * 1e3),
                       "checksum": float(sc.double().sum()), "idx_sum": int(idx.sum())}), flush=True)
 
 
 if __name__ == "__main__":
     if os.environ.get("EVR_PROBE_CHILD"):
-        one(int(os.environ.get("EVR_PROBE_Q", "10000")))
+        one(int(os.environ.get("EVR_PROBE_Q", "10000")), int(os.environ.get("EVR_PROBE_N", "10000000")),
+            int(os.environ.get("EVR_PROBE_ITERS", "8")))
     else:
         for setting in sys.argv[1:] or [""]:
             env = dict(os.environ, EVR_PROBE_CHILD="1", EVR_PROBE_LABEL=setting)
