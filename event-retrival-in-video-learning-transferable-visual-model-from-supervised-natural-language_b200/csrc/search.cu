@@ -112,6 +112,8 @@ struct ScanArgs {
   int stages;          // depth of the store-row smem ring actually used (<= kScanStages; 2 at D = 768)
   int row_evict_last;  // A/B knob (EVR_SCAN_EVICT_LAST=1): store rows stay in L2 as long as possible
   int tile_stride;     // sample pass: tile t of the launch reads store tile t * tile_stride (1 in the full scan)
+  int* sched_counter;  // dynamic item distribution (nullptr: static round-robin): next unclaimed item, zeroed per call
+  unsigned long long* sched_tickets;  // [units][kSchedDepth]: (k + 1) << 32 | item claimed for the unit's k-th step
   int qt_group;        // query tiles that walk the store together (a pass); num_qt = one pass (items slice-major)
   int rotate;          // 1: the query tiles of a pass start a slice at different tiles (and wrap around)
 };
@@ -133,6 +135,41 @@ __device__ __forceinline__ ScanItem scan_item(const ScanArgs& a, int item) {
   r.qt = pass * G + r.lane_in_group;
   return r;
 }
+// Dynamic item distribution.  With a static round-robin the units' positions drift apart for good (SMs differ by a
+// per cent or so in speed: 170 slices over a 100 M-row scan), fast units then stand at the ring flags of slow ones and
+// the scan loses 8-10 %; a deeper ring only moves the point where that starts.  Here the producer thread of a unit's
+// leader CTA claims the next item with an atomic add -- one step ahead, so the round trip is off the critical path --
+// and publishes it as a (step, item) ticket in global memory that the unit's other roles (peer producer, MMA issuer,
+// epilogue warps) read when they get to that step.  Items are claimed in increasing order, so every unit stays within
+// a round of the others, the slices being read stay the same few for all units, and the ring stays shallow.
+constexpr int kSchedDepth = 8;   // tickets per unit; the roles of a unit are never more than ~3 items apart
+__device__ __forceinline__ int sched_claim(const ScanArgs& a, int unit, int k, int num_items) {
+  int item = atomicAdd(a.sched_counter, 1);
+  if (item >= num_items) item = -1;
+  const unsigned long long word = (static_cast<unsigned long long>(k + 1) << 32) | static_cast<unsigned>(item);
+  unsigned long long* t = a.sched_tickets + static_cast<size_t>(unit) * kSchedDepth + (k & (kSchedDepth - 1));
+  asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(t), "l"(word) : "memory");
+  return item;
+}
+__device__ __forceinline__ int sched_read(const ScanArgs& a, int unit, int k) {
+  const unsigned long long* t = a.sched_tickets + static_cast<size_t>(unit) * kSchedDepth + (k & (kSchedDepth - 1));
+  unsigned long long w;
+  unsigned spins = 0;
+  while (true) {
+    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(w) : "l"(t) : "memory");
+    if (static_cast<unsigned>(w >> 32) == static_cast<unsigned>(k + 1)) break;
+    __nanosleep(100);
+    if (++spins > (1u << 25)) asm volatile("trap;");   // seconds: a protocol bug traps instead of hanging
+  }
+  return static_cast<int>(static_cast<unsigned>(w));
+}
+// step k of a unit's walk -> item (or -1: done)
+__device__ __forceinline__ int sched_item(const ScanArgs& a, int unit, int num_units, int k, int num_items) {
+  if (a.sched_counter != nullptr) return sched_read(a, unit, k);
+  const long long it = unit + static_cast<long long>(k) * num_units;
+  return it < num_items ? static_cast<int>(it) : -1;
+}
+
 // tile visited at step i of an item's walk over [t0, t1)
 __device__ __forceinline__ int64_t scan_tile(const ScanArgs& a, const ScanItem& it, int64_t t0, int64_t t1, int64_t i) {
   if (!a.rotate) return t0 + i;
@@ -252,7 +289,17 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       uint32_t phase = 0, qphase = 0;
       uint64_t row_policy = args.num_qt > 1 ? kEvictNormal : kEvictFirst;
       if (args.row_evict_last) row_policy = kEvictLast;
-      for (int item = unit; item < num_items; item += num_units) {
+      const bool claims = args.sched_counter != nullptr && leader;   // this thread distributes the unit's items
+      int next_item = claims ? sched_claim(args, unit, 0, num_items) : 0;
+      for (int k = 0;; ++k) {
+        int item;
+        if (claims) {
+          item = next_item;
+          if (item >= 0) next_item = sched_claim(args, unit, k + 1, num_items);   // one step ahead
+        } else {
+          item = sched_item(args, unit, num_units, k, num_items);
+        }
+        if (item < 0) break;
         const ScanItem si = scan_item(args, item);
         const int qt = si.qt, slice = si.slice;
         mbar_wait(q_empty, qphase ^ 1);  // MMAs of the previous item no longer read the query tile
@@ -297,7 +344,9 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       int stage = 0, as = 0;
       uint32_t phase = 0, aphase = 0, qphase = 0;
       const uint32_t q_addr = smem_u32(smem_q);
-      for (int item = unit; item < num_items; item += num_units) {
+      for (int k = 0;; ++k) {
+        const int item = sched_item(args, unit, num_units, k, num_items);
+        if (item < 0) break;
         const int slice = scan_item(args, item).slice;
         mbar_wait(q_full, qphase);
         qphase ^= 1;
@@ -338,7 +387,11 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     const int trigger = cap - kRowTile;
     int as = 0;
     uint32_t aphase = 0;
-    for (int item = unit; item < num_items; item += num_units) {
+    for (int step = 0;; ++step) {
+      int item = 0;
+      if (lane == 0) item = sched_item(args, unit, num_units, step, num_items);
+      item = __shfl_sync(0xffffffffu, item, 0);
+      if (item < 0) break;
       const ScanItem si = scan_item(args, item);
       const int qt = si.qt, slice = si.slice;
       const int q0 = (qt * CG + static_cast<int>(rank)) * kScanQTile + quad * 32;  // first query of this warp
@@ -871,7 +924,7 @@ struct ScanPlan {
   int64_t n0;   // rows of the sample pass (0: none)
   int groups;   // n0 / 64
   int select_cap;  // candidate keys the select kernel can hold in shared memory
-  size_t lists_bytes, counts_bytes, gmax_bytes, thresh_bytes, lthresh_bytes, done_bytes, total_bytes;
+  size_t lists_bytes, counts_bytes, gmax_bytes, thresh_bytes, lthresh_bytes, done_bytes, sched_bytes, total_bytes;
 };
 
 static size_t up256(size_t x) { return (x + 255) & ~size_t(255); }
@@ -951,12 +1004,9 @@ static void plan_core(int64_t N, int D, int Q, int k, int sm_total, ScanCore* p)
   // different moments, to pull the units that share a slice apart: DRAM reads 80-113 GB at ring 10, 21-29 GB at 20,
   // 15-20 GB at 32, 14.5 GB at 48 for the 10.24 GB store; 32 lists of 4 KB per query = 1.3 GB of workspace at Q = 10 000)
   int ring = 2 * conc + 28;
-  // The units' positions are a random walk, so a longer scan needs a deeper ring to stay clear of the flags: 50 M rows,
-  // Q = 10 000: 447 ms at ring 32, 422 at 64, 391 at 96 (= the per-row time of the 10 M scan), 395 at 128.
-  if (N > 10000000) {
-    const int64_t over = N - 10000000 < 40000000 ? N - 10000000 : 40000000;
-    ring += static_cast<int>(64 * over / 40000000);
-  }
+  // (With the static round-robin of round 2's first half the depth had to grow with the scan -- 50 M rows: 447 ms at
+  // ring 32, 391 at 96; 100 M rows: 933 ms at 96, 845 at 224 -- because the units drift apart for good; with the items
+  // claimed dynamically, see sched_claim, 32 is enough at every size: 50 M rows 384 ms, 100 M rows 758 ms.)
   if (const char* e = getenv("EVR_SCAN_RING")) {   // experiments: how far the units may drift apart, in slices
     if (atoi(e) > 0) ring = atoi(e);
   }
@@ -1010,8 +1060,9 @@ static int plan_scan(int64_t N, int D, int Q, int k, ScanPlan* p) {
   p->done_bytes = up256(static_cast<size_t>(p->main.q_pad / 32) * p->main.num_slices * sizeof(unsigned));
   p->gmax_bytes = p->n0 > 0 ? up256(static_cast<size_t>(p->main.q_pad) * p->groups * sizeof(float)) : 0;
   p->thresh_bytes = up256(static_cast<size_t>(p->main.q_pad) * sizeof(float));
+  p->sched_bytes = up256(256 + 160 * kSchedDepth * sizeof(unsigned long long));   // item counter + tickets of <= 160 units
   p->total_bytes = p->lists_bytes + p->counts_bytes + p->gmax_bytes + p->thresh_bytes + p->lthresh_bytes +
-                   p->done_bytes + 256;
+                   p->done_bytes + p->sched_bytes + 256;
   return 0;
 }
 
@@ -1084,8 +1135,10 @@ extern "C" int evr_topk_workspace_bytes(int64_t N, int D, int Q, int k, size_t* 
 // in temporal order still yields a representative threshold; tile_stride = 1 and N_store = N for the full scan).
 static int run_scan(const ScanCore& c, const void* store, int64_t N, int64_t N_store, int tile_stride, int D,
                     const void* queries, int Q, int k, const float* init_thresh, int2* lists, int* counts,
-                    float* list_thresh, unsigned* done, unsigned epoch, float* group_max, int groups, cudaStream_t s) {
+                    float* list_thresh, unsigned* done, unsigned epoch, float* group_max, int groups, cudaStream_t s,
+                    int* sched_counter = nullptr, unsigned long long* sched_tickets = nullptr) {
   ScanArgs a{};
+  a.sched_counter = sched_counter; a.sched_tickets = sched_tickets;
   a.N = N; a.D = D; a.Q = Q; a.k = k; a.tile_stride = tile_stride;
   { const char* e = getenv("EVR_SCAN_EVICT_LAST"); a.row_evict_last = (e && e[0] == '1' && c.num_qt > 1) ? 1 : 0; }
   a.num_qt = c.num_qt; a.num_slices = c.num_slices; a.tiles_per_slice = c.tiles_per_slice; a.q_pad = c.q_pad;
@@ -1151,8 +1204,18 @@ extern "C" int evr_topk_search(const void* store, int64_t N, int D, int64_t row_
   static std::atomic<unsigned> epoch_counter{0};
   unsigned epoch = epoch_counter.fetch_add(1, std::memory_order_relaxed) + 1;
   if (epoch == 0) epoch = epoch_counter.fetch_add(1, std::memory_order_relaxed) + 1;   // 0 is what fresh memory holds
+  // dynamic item distribution for the multi-tile plans (a single query tile has one slice per SM: nothing to balance)
+  int* sched_counter = nullptr;
+  unsigned long long* sched_tickets = nullptr;
+  static const bool static_items = [] { const char* e = getenv("EVR_SCAN_STATIC"); return e && e[0] == '1'; }();
+  if (p.main.num_qt > 1 && !static_items && p.main.grid / p.main.cg <= 160) {
+    uint8_t* sched = reinterpret_cast<uint8_t*>(done) + p.done_bytes;
+    EVR_CHECK_CUDA(cudaMemsetAsync(sched, 0, p.sched_bytes, s));
+    sched_counter = reinterpret_cast<int*>(sched);
+    sched_tickets = reinterpret_cast<unsigned long long*>(sched + 256);
+  }
   if (int r = run_scan(p.main, store, N, N, 1, D, queries, Q, k, init, lists, counts, lthresh, done, epoch, nullptr, 0,
-                       s)) return r;
+                       s, sched_counter, sched_tickets)) return r;
   SelectArgs sa{};
   sa.lists = lists; sa.counts = counts;
   sa.P = p.main.ring; sa.q_pad = p.main.q_pad; sa.cap = p.main.cap; sa.k = k; sa.smem_cap = p.select_cap;
