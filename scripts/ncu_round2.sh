@@ -26,4 +26,5 @@ ncu --set full --clock-control none --import-source on -k regex:attention_tc -s 
 ncu --set full --clock-control none --import-source on -k regex:layernorm -s 3 -c 1 -o $O/${P}_prof_ln -f python scripts/prof_case.py encode 1 > $O/ncu_ln.log 2>&1
 python scripts/prof_case.py scan_small 1 > $O/plain_scan_small1.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:topk_scan -s 1 -c 1 -o $O/${P}_prof_scan_small -f python scripts/prof_case.py scan_small 1 > $O/ncu_scan_small_full.log 2>&1
+bash scripts/scan_l2_breakdown.sh c3_${T} 10000 > $O/${P}_scan_c3_l2.txt 2>&1
 ls -la $O | grep ${P}
