@@ -348,3 +348,32 @@ def test_full_size_cta_pair_path(pkg, cuda):
     for j, p in enumerate(pick.tolist()):
         assert so.topk_equal_up_to_ties(idx[p].cpu().numpy(), sc[p].cpu().numpy(), ref_i[j].cpu().numpy(),
                                         ref_s[j].cpu().numpy(), 1e-5), p
+
+
+@pytest.mark.parametrize("N,Q,k", [(400_000, 19_201, 10),    # 76 query tiles of 256: more tiles than CTA pairs
+                                   (1_200_000, 3_329, 100),  # 14 tiles (13 full + 1 of one query), many slices, ring wraps
+                                   (90_000, 5_000, 37)])      # 20 tiles over a handful of slices: more units than items at the end
+def test_many_query_tiles_dynamic_items(pkg, cuda, N, Q, k):
+    """The multi-tile plans hand their (query tile, slice) items out dynamically (one atomic counter per call, tickets
+    published by the leader CTA's producer thread).  Whatever order the units take them in, the lists must equal a
+    chunked fp32 scan of the same operands (up to ties inside 1e-5) for sampled queries of every query tile, planted
+    rows must come first, and two calls on the same workspace must agree bit for bit."""
+    g = torch.Generator(device=cuda).manual_seed(N + Q)
+    rows = torch.randn((N, 512), generator=g, device=cuda)
+    rows = (rows / rows.norm(dim=-1, keepdim=True)).half()
+    q = torch.randn((Q, 512), generator=g, device=cuda)
+    q = (q / q.norm(dim=-1, keepdim=True)).half()
+    planted = torch.randperm(N, generator=g, device=cuda)[:Q]
+    rows[planted] = q
+    store = pkg.search.FrameStore(rows)
+    sc, idx = store.search(q, k)
+    sc2, idx2 = store.search(q, k)
+    assert torch.equal(idx, idx2) and torch.equal(sc, sc2)
+    assert torch.equal(idx[:, 0], planted)
+    assert torch.all(sc[:, 1:] <= sc[:, :-1]) and int(idx.min()) >= 0 and int(idx.max()) < N
+    pick = torch.arange(0, Q, max(1, Q // 96), device=cuda)      # a few queries of every 256-query tile
+    ref_s, ref_i = _torch_reference_topk(rows, q[pick], k, chunk=200_000)
+    assert torch.allclose(sc[pick], ref_s, atol=1e-5)
+    for j, p in enumerate(pick.tolist()):
+        assert so.topk_equal_up_to_ties(idx[p].cpu().numpy(), sc[p].cpu().numpy(), ref_i[j].cpu().numpy(),
+                                        ref_s[j].cpu().numpy(), 1e-5), p
