@@ -973,14 +973,12 @@ static void plan_core(int64_t N, int D, int Q, int k, int sm_total, ScanCore* p)
       if (eff >= 0.97 * best_eff) { best = s; break; }
     }
     S = best;
-    // A slice is read by all num_qt query tiles, on different units.  Nothing keeps those units in step, so over a
-    // 277 MB slice (10 M rows / 37) they drift further apart than L2 can hold and most of them fetch their rows from
-    // HBM on their own: ncu measured 136.6 GB of DRAM reads for a 10.24 GB store at Q = 10 000 (62 % L2 hit rate).
-    // Slices are therefore small -- everything in flight at one time, ceil(units / num_qt) consecutive slices, is a few
-    // MB -- and issued slice-major, so the units reading a slice are never more than a few slices apart.  Measured
-    // (profiles/r02_scan_c3_traffic.txt): 73-82 GB and 10 % less time; the hit rate stays near 72 % whatever the slice
-    // size (6-48 MB in flight) and whether or not the units are skewed against each other inside a slice, i.e. what is
-    // left is not a capacity effect (the missing step is a TMA-multicast cluster sharing each row tile).
+    // A slice is read by all num_qt query tiles, on different units.  Over round 1's 277 MB slices (10 M rows / 37) the
+    // units drifted further apart than L2 can hold and most of them fetched their rows from HBM on their own: ncu
+    // measured 136.6 GB of DRAM reads for a 10.24 GB store at Q = 10 000.  Slices are therefore small -- everything in
+    // flight at one time, ceil(units / num_qt) consecutive slices, is a few MB -- and handed out in slice-major order
+    // (dynamically, see sched_claim), so the units reading a slice are never more than a round apart: 11 GB of DRAM
+    // reads (profiles/r02_i_scan_c3_l2.txt).  6-96 MB in flight all measure the same.
     const int conc = (sms + p->qt_group - 1) / p->qt_group;
     int64_t inflight_mb = 12;
     if (const char* e = getenv("EVR_SCAN_INFLIGHT_MB")) {   // tuning knob
