@@ -30,8 +30,12 @@ def metrics_from_ranks(ranks):
 
 def full_ranking(store_rows, queries, device="cuda", query_chunk=256):
     """[Q, N] int64: row ids of `store_rows` in descending cosine for every query (both are L2-normalised here)."""
-    store = FrameStore.from_tensor(torch.as_tensor(store_rows), device=device)
-    q = torch.as_tensor(queries)
+    rows, q = torch.as_tensor(store_rows), torch.as_tensor(queries)
+    pad = (-rows.shape[1]) % 64        # the scan takes widths that are multiples of 64: zero columns change no dot product
+    if pad:
+        rows = torch.nn.functional.pad(rows, (0, pad))
+        q = torch.nn.functional.pad(q, (0, pad))
+    store = FrameStore.from_tensor(rows, device=device)
     out = []
     for i in range(0, q.shape[0], query_chunk):
         out.append(store.search(q[i:i + query_chunk], store.N)[1])
@@ -48,10 +52,13 @@ def positions_of(ranking, targets):
 
 def evaluate_retrieval(image_features, text_features, caption_image, device="cuda"):
     """image_features [I, D], text_features [T, D] (any float dtype, normalised or not), caption_image [T]: index of the
-    image each caption describes -> {"t2i": {...}, "i2t": {...}, "mean": {..., "rsum"}, "t2i_ranks", "i2t_ranks"}."""
+    image each caption describes (-1: its image is not in the set) -> {"t2i": {...}, "i2t": {...},
+    "mean": {..., "rsum"}, "t2i_ranks", "i2t_ranks"}."""
     caption_image = np.asarray(caption_image, dtype=np.int64)
-    t2i_ranks = positions_of(full_ranking(image_features, text_features, device), caption_image)
-    images_with_captions = np.unique(caption_image)            # compare_models.py:1052-1054 skips images without one
+    known = np.nonzero(caption_image >= 0)[0]     # a caption of an image outside the set is skipped (:1007) ...
+    t2i_ranks = positions_of(full_ranking(image_features, torch.as_tensor(text_features)[known], device),
+                             caption_image[known])
+    images_with_captions = np.unique(caption_image[known])     # ... but still competes in i2t; :1052-1054 skips images without a caption
     order = full_ranking(text_features, torch.as_tensor(image_features)[images_with_captions], device)
     pos = torch.empty_like(order)
     pos.scatter_(1, order, torch.arange(order.shape[1], device=order.device).expand_as(order))   # caption -> position
