@@ -964,11 +964,13 @@ def frame_metadata_items(folder_path, output_json_path, path_video):
     items = []
     for name in sorted(f for f in os.listdir(folder_path) if f.endswith(IMAGE_EXT)):   # the rows of the ingest, exactly
         path = os.path.join(folder_path, name)
-        with Image.open(path) as im:
+        with Image.open(path) as im:   # get_image_metadata, JSON_sample_DOC.py:12-26
             width, height = im.size
+            metadata = {"size_bytes": os.path.getsize(path), "mime_type": Image.MIME.get(im.format, "unknown"),
+                        "width": width, "height": height, "num_channels": len(im.getbands())}
         stem = os.path.splitext(name)[0]
         items.append({"id": str(uuid.uuid4()), "media_type": "image", "filepath": path, "tags": ["MainData"],
-                      "metadata": {"width": width, "height": height}, "video": path_video, "frameid": name,
+                      "metadata": metadata, "video": path_video, "frameid": name,
                       "text_detections": {"detections": []}, "object_detections": {"detections": []},
                       "frameidx": int(stem) if stem.isdigit() else None})
     os.makedirs(os.path.dirname(output_json_path) or ".", exist_ok=True)

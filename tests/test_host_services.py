@@ -186,6 +186,40 @@ def test_frame_metadata_items_layout(services, tmp_path):
     first = items[0]
     assert set(first) == {"id", "media_type", "filepath", "tags", "metadata", "video", "frameid", "text_detections",
                           "object_detections", "frameidx"}
-    assert first["metadata"] == {"width": 32, "height": 18} and first["video"] == "/videos/v.mp4"
+    assert first["metadata"]["width"] == 32 and first["metadata"]["height"] == 18 and first["video"] == "/videos/v.mp4"
+    assert set(first["metadata"]) == {"size_bytes", "mime_type", "width", "height", "num_channels"}   # :15-21
     assert {i["frameid"]: i["frameidx"] for i in items} == {"1061.jpg": 1061, "300.jpg": 300, "7.jpg": 7,
                                                            "cover.png": None}
+
+
+def test_metadata_items_equal_the_references(services, tmp_path):
+    """`frame_metadata_items` against tests/golden/ref_metadata_golden.json: the items the reference's own
+    `process_image` / `get_image_metadata` (JSON_sample_DOC.py:12-87, run unmodified with detectors that find nothing)
+    wrote for its own key-frames -- same keys in the same order, same values, `id` apart (a fresh uuid4 each)."""
+    import shutil
+    import uuid
+    golden_dir = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    with open(os.path.join(golden_dir, "ref_metadata_golden.json"), encoding="utf-8") as f:
+        want = json.load(f)["items"]
+    frames = tmp_path / "Violence"
+    frames.mkdir()
+    for name in os.listdir(os.path.join(golden_dir, "ref_frames")):
+        if name.endswith(".jpg"):
+            shutil.copyfile(os.path.join(golden_dir, "ref_frames", name), frames / name)
+    (frames / "7.jpg").write_bytes((frames / want[0]["frameid"]).read_bytes())     # a numeric stem: frameidx = 7
+    (frames / "notes.txt").write_text("not a frame")
+    out = services.frame_metadata_items(str(frames), str(tmp_path / "meta" / "Violence_metadata.json"),
+                                        "/videos/Violence.mp4")
+    with open(out, encoding="utf-8") as f:
+        got = json.load(f)
+    assert [g["frameid"] for g in got] == sorted([w["frameid"] for w in want] + ["7.jpg"])
+    by_name = {g["frameid"]: g for g in got}
+    for w in want:
+        g = by_name[w["frameid"]]
+        assert list(g) == list(w)                                   # key order as the reference writes it
+        assert uuid.UUID(g["id"]).version == 4
+        assert os.path.basename(g["filepath"]) == w["filepath"] and os.path.isabs(g["filepath"])
+        for key in w:
+            if key not in ("id", "filepath"):
+                assert g[key] == w[key], (w["frameid"], key)
+    assert by_name["7.jpg"]["frameidx"] == 7 and by_name[want[0]["frameid"]]["frameidx"] is None
