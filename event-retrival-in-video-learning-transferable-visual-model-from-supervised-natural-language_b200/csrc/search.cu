@@ -142,7 +142,8 @@ __device__ __forceinline__ ScanItem scan_item(const ScanArgs& a, int item) {
 // and publishes it as a (step, item) ticket in global memory that the unit's other roles (peer producer, MMA issuer,
 // epilogue warps) read when they get to that step.  Items are claimed in increasing order, so every unit stays within
 // a round of the others, the slices being read stay the same few for all units, and the ring stays shallow.
-constexpr int kSchedDepth = 8;   // tickets per unit; the roles of a unit are never more than ~3 items apart
+constexpr int kSchedDepth = 16;  // tickets per unit.  A slot is reused 16 steps later; the producer is at most 6 shared-memory
+                                 // stages + 4 accumulators = 10 row tiles = 5 two-tile items (D = 64) ahead of the epilogue warps
 __device__ __forceinline__ int sched_claim(const ScanArgs& a, int unit, int k, int num_items) {
   int item = atomicAdd(a.sched_counter, 1);
   if (item >= num_items) item = -1;
