@@ -103,6 +103,7 @@ int launch_gemm_bf16(const void* A, int lda, const void* W, int ldw, const GemmA
   const int tiles = num_m * ((args.N + bn - 1) / bn);
   GemmArgs ga = args;
   ga.prof = prof_device_slot(PF_GEMM);
+  ga.reverse_m = args.reverse_m;
   ga.tail_split = choose_tail_split(tiles, units, bn);
   ga.full_tiles = ga.tail_split > 1 ? tiles - tiles % units : tiles;
   const int items = ga.full_tiles + (tiles - ga.full_tiles) * ga.tail_split;

@@ -40,6 +40,7 @@ struct GemmArgs {
   // evr_profile_enable(2): [0] = earliest %globaltimer at which a CTA got past pdl_wait, [1] = latest CTA exit; nullptr
   // otherwise.  Times the launch in place (PDL overlap intact), without a stream operation between the kernels.
   unsigned long long* prof;
+  int reverse_m;      // 1: row blocks are walked from the last to the first (launch_gemm_bf16 decides)
 };
 
 // work item -> (tile, first column, width); items [0, full_tiles) are whole tiles, then tail_split strips per tile
@@ -47,7 +48,8 @@ struct GemmItem {
   int m_idx, n0, width;
 };
 template <int BLOCK_N>
-__device__ __forceinline__ GemmItem gemm_item(int it, int num_n, int full_tiles, int tail_split) {
+__device__ __forceinline__ GemmItem gemm_item(int it, int num_n, int full_tiles, int tail_split, int num_m = 0,
+                                              int reverse_m = 0) {
   GemmItem g;
   int tile = it, sub = 0;
   g.width = BLOCK_N;
@@ -57,8 +59,9 @@ __device__ __forceinline__ GemmItem gemm_item(int it, int num_n, int full_tiles,
     sub = j - (j / tail_split) * tail_split;
     g.width = BLOCK_N / tail_split;
   }
-  g.m_idx = tile / num_n;  // n-fast: the N tiles of one row block run together, A is read from HBM once
-  g.n0 = (tile - g.m_idx * num_n) * BLOCK_N + sub * g.width;
+  const int m_walk = tile / num_n;  // n-fast: the N tiles of one row block run together, A is read from HBM once
+  g.m_idx = reverse_m ? num_m - 1 - m_walk : m_walk;
+  g.n0 = (tile - m_walk * num_n) * BLOCK_N + sub * g.width;
   return g;
 }
 
@@ -183,7 +186,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       int stage = 0;
       uint32_t phase = 0;
       for (int it = unit; it < num_items; it += num_units) {
-        const GemmItem g = gemm_item<BLOCK_N>(it, num_n, args.full_tiles, args.tail_split);
+        const GemmItem g = gemm_item<BLOCK_N>(it, num_n, args.full_tiles, args.tail_split, num_m, args.reverse_m);
         const int a_row = g.m_idx * kTileM + static_cast<int>(rank) * kGemmBlockM;
         const int b_rows = g.width / CG;  // weight rows staged by this CTA
         const int b_row = g.n0 + static_cast<int>(rank) * b_rows;
@@ -260,7 +263,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     int as = 0;
     uint32_t aphase = 0;
     for (int it = unit; it < num_items; it += num_units) {
-      const GemmItem g = gemm_item<BLOCK_N>(it, num_n, args.full_tiles, args.tail_split);
+      const GemmItem g = gemm_item<BLOCK_N>(it, num_n, args.full_tiles, args.tail_split, num_m, args.reverse_m);
       const int row0 = g.m_idx * kTileM + static_cast<int>(rank) * kGemmBlockM + q * 32;  // first row of this warp
       const int col_base = g.n0 + hsel * kEpiCols;
       const int n_lim = min(args.N, g.n0 + g.width);  // columns of this item (a tail strip is narrower than BLOCK_N)

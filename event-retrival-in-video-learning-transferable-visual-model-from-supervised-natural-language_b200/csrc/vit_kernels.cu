@@ -114,13 +114,18 @@ int launch_cls_rows(float* x, const float* cls, const float* pos, int B, int L, 
 template <int D4, bool OUT_BF16>
 __global__ void __launch_bounds__(256)
 layernorm_kernel(const float* in, size_t in_stride, void* out, size_t out_stride,  // in may alias out (ln_pre)
-                 const float* __restrict__ gamma, const float* __restrict__ beta, int rows, unsigned long long* prof) {
+                 const float* __restrict__ gamma, const float* __restrict__ beta, int rows, int reverse,
+                 unsigned long long* prof) {
   pdl_launch_dependents();
   pdl_wait();
   prof_stamp_begin(prof);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int row = blockIdx.x * 8 + warp;
+  int row = blockIdx.x * 8 + warp;
   if (row >= rows) return;
+  // A residual stream larger than L2 was last written front to back (the residual GEMM walks its row blocks in order),
+  // so its END is what L2 still holds: walking it back to front turns those lines into hits, front to back every line
+  // has been evicted by the time it is reached.
+  if (reverse) row = rows - 1 - row;
   constexpr int d = D4 * 128;
   const float4* x4 = reinterpret_cast<const float4*>(in + static_cast<size_t>(row) * in_stride);
   float4 v[D4];
@@ -171,15 +176,18 @@ int launch_layernorm(const float* in, size_t in_stride, void* out, size_t out_st
   const int blocks = (rows + 7) / 8;
   ProfScope ps(PF_LN, stream);
   unsigned long long* prof = prof_device_slot(PF_LN);
+  static const int reverse_mode = [] { const char* e = getenv("EVR_LN_REVERSE"); return e ? atoi(e) : -1; }();   // -1: auto
+  const int reverse = reverse_mode >= 0 ? reverse_mode
+                                        : (static_cast<size_t>(rows) * d * 4 > (96u << 20) && in_stride == static_cast<size_t>(d));
   if (d == 512) {
-    if (out_bf16) EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<4, true>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows, prof));
-    else EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<4, false>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows, prof));
+    if (out_bf16) EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<4, true>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows, reverse, prof));
+    else EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<4, false>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows, reverse, prof));
   } else if (d == 768) {
-    if (out_bf16) EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<6, true>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows, prof));
-    else EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<6, false>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows, prof));
+    if (out_bf16) EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<6, true>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows, reverse, prof));
+    else EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<6, false>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows, reverse, prof));
   } else {
-    if (out_bf16) EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<8, true>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows, prof));
-    else EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<8, false>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows, prof));
+    if (out_bf16) EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<8, true>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows, reverse, prof));
+    else EVR_CHECK_CUDA(launch_pdl(layernorm_kernel<8, false>, dim3(blocks), dim3(256), 0, stream, in, in_stride, out, out_stride, gamma, beta, rows, reverse, prof));
   }
   EVR_CHECK_LAUNCH();
   return 0;
