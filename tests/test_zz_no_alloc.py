@@ -89,3 +89,28 @@ def test_static_scratch_scan_rejects_what_does_not_fit(pkg, cuda):
     s2, i2 = torch.empty_like(ref_scores), torch.empty_like(ref_idx)
     _search_static(pkg, store, q[:8], 20, 0, s2, i2)
     assert torch.equal(i2, ref_idx) and torch.equal(s2, ref_scores)
+
+
+def test_static_scratch_scan_under_graph_capture(pkg, cuda):
+    """The use the entry point was asked for: captured into a CUDA graph (global capture mode: a cudaMalloc anywhere in
+    the call would fail the capture) and replayed with new query contents in the same buffers.  Every replay runs the
+    captured clears of the counters and flags first, so it must equal a fresh `evr_topk_search` each time."""
+    store = _unit_rows(120_000, 512, 51, cuda)
+    q = _unit_rows(32, 512, 52, cuda)
+    k = 25
+    scores = torch.empty((32, k), device=cuda)
+    idx = torch.empty((32, k), dtype=torch.int64, device=cuda)
+    _search_static(pkg, store, q, k, 7, scores, idx)            # set-up outside the capture (symbol address, attributes)
+    L = pkg._lib
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        L.check(L.lib.evr_topk_search_static(L.ptr(store), store.shape[0], 512, 7, L.ptr(q), 32, k, L.ptr(scores),
+                                             L.ptr(idx), L.current_stream_ptr()), "evr_topk_search_static")
+    for seed in (53, 54, 55):
+        q.copy_(_unit_rows(32, 512, seed, cuda))
+        scores.fill_(float("nan"))
+        idx.fill_(-7)
+        graph.replay()
+        torch.cuda.synchronize()
+        ref_scores, ref_idx, _ = _search(pkg, store, q, k, 7)
+        assert torch.equal(idx, ref_idx) and torch.equal(scores, ref_scores), seed
